@@ -1,0 +1,277 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path: RNS negacyclic NTT+INTT throughput.
+
+Workload (BASELINE.json configs[1]): N = 2^16, L = 32 sixty-bit primes of Phantom's
+CoeffModulus::Create, batch 64 polys = 2048 limb-polys = 1 GiB of u64, synthetic
+splitmix64 coefficients.  One step = forward NTT + inverse NTT of the whole batch, in place.
+metric = limb-polys/s through NTT+INTT (a limb-poly counts once per NTT+INTT pair).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` is device-resident throughput (CUDA events on the
+launch stream, max over ranks); `e2e` is the same metric through the C-ABI host-buffer entry
+points (pinned host memory, H2D and D2H inside the timed region).  `--impl reference` times
+the CPU restatement of the reference algorithm (oracle/, OpenMP over all host threads) on a
+bounded sample of the same workload: the reference has no CPU implementation of its own.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LOGN, LIMBS, BATCH, BITS = 16, 32, 64, 60
+N = 1 << LOGN
+LIMB_POLYS = LIMBS * BATCH
+ALGO_BYTES_PER_TRANSFORM = 16 * N                # 8 B read + 8 B write per coefficient
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_sample(sample_limb_polys: int, reps: int):
+    """Oracle (CPU restatement of the reference algorithm) on a bounded sample, all host threads."""
+    import oracle as O
+    mods = O.coeff_modulus_create(N, BITS, LIMBS)
+    t = O.PhantomTables(LOGN, mods)
+    polys = max(1, sample_limb_polys // LIMBS)
+    x = O.synth_polys(42, polys, mods, N)
+    lib = O.lib()
+    flat = x.reshape(-1)
+    args_f = (flat, polys, LIMBS, LOGN, t.moduli, t.tw.reshape(-1), t.tws.reshape(-1))
+    args_i = (flat, polys, LIMBS, LOGN, t.moduli, t.itw.reshape(-1), t.itws.reshape(-1), t.n_inv, t.n_inv_shoup)
+    lib.mfo_negacyclic_forward_batch(*args_f); lib.mfo_negacyclic_inverse_batch(*args_i)     # warm
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        lib.mfo_negacyclic_forward_batch(*args_f)
+        lib.mfo_negacyclic_inverse_batch(*args_i)
+        times.append(time.perf_counter() - t0)
+    assert (flat.reshape(x.shape) == O.synth_polys(42, polys, mods, N)).all()
+    return polys * LIMBS, times, lib.mfo_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_lp, times, cores = cpu_sample(4 * LIMBS, max(1, args.steps))
+    for _ in range(0):
+        pass
+    ms = 1e3 * sum(times) / len(times)
+    value = n_lp / (sum(times) / len(times))
+    sample = f"{n_lp} limb-polys ({n_lp // LIMBS} of {BATCH} polys x {LIMBS} limbs) per step, NTT+INTT, OpenMP"
+    line = {
+        "impl": "reference", "metric": "ntt_intt_limb_polys_per_s", "value": value, "unit": "limb-polys/s",
+        "n_gpus": args.gpus, "steps": len(times), "warmup": 1, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": f"N=2^{LOGN} L={LIMBS} batch={BATCH} negacyclic NTT+INTT, {BITS}-bit primes",
+                   "note": "CPU restatement of the reference algorithm (oracle/); the reference ships no CPU path"},
+        "cpu_baseline": {"value": value, "unit": "limb-polys/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "limb-polys/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--chunk", type=int, default=int(os.environ.get("MFHE_CHUNK", "-1")),
+                    help="limb-polys per kernel pair (L2-resident chunking); -1 = library default")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import matrix_fhe_gpu_b200 as m
+    import oracle as O          # inputs + cpu_baseline + one-poly self-check only
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    mods = O.coeff_modulus_create(N, BITS, LIMBS)
+    plan = m.NttPlan(LOGN, mods)
+    if args.chunk >= 0:
+        plan.set_chunk(args.chunk)
+    # synthetic input, each rank its own batch (weak scaling over the batch axis, no collective)
+    x = O.synth_polys(42 + rank, BATCH, mods, N)
+    d = torch.from_numpy(x.view(np.int64)).to(dev)
+    stream = torch.cuda.current_stream()
+
+    def step():
+        plan.forward_(d, stream)
+        plan.inverse_(d, stream)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    # correctness guard inside the bench: after W round trips poly 0 is still the input
+    assert (d[0].cpu().numpy().view(np.uint64) == x[0]).all(), "round trip failed"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    fwd_ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev[0].record(stream)
+    for _ in range(args.steps):
+        step()
+    ev[1].record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = ev[0].elapsed_time(ev[1])
+    # per-transform durations (forward = column+row kernels, inverse = row+column kernels)
+    tf, ti = [], []
+    for _ in range(10):
+        fwd_ev[0].record(stream); plan.forward_(d, stream)
+        fwd_ev[1].record(stream); plan.inverse_(d, stream)
+        fwd_ev[2].record(stream); torch.cuda.synchronize()
+        tf.append(fwd_ev[0].elapsed_time(fwd_ev[1])); ti.append(fwd_ev[1].elapsed_time(fwd_ev[2]))
+    t = torch.tensor([ms_total], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    value = world * LIMB_POLYS / (ms_step * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers (pinned), copies inside the timing
+    hbuf = torch.from_numpy(x.view(np.int64).copy()).pin_memory()
+    hnp = hbuf.numpy().view(np.uint64)
+    plan.forward_host_(hnp); plan.inverse_host_(hnp)        # warm (allocates staging)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        plan.forward_host_(hnp)
+        plan.inverse_host_(hnp)
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / args.e2e_steps
+    te = torch.tensor([e2e_s], device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te.item())
+    assert (hnp.reshape(x.shape)[0] == x[0]).all()
+    nbytes = x.nbytes
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        t_fwd = statistics.median(tf) * 1e-3
+        t_inv = statistics.median(ti) * 1e-3
+        algo = ALGO_BYTES_PER_TRANSFORM * LIMB_POLYS
+        worst = max(t_fwd, t_inv)
+        achieved = algo / worst / 1e9
+        line = {
+            "metric": "ntt_intt_limb_polys_per_s", "value": value, "unit": "limb-polys/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": f"N=2^{LOGN} L={LIMBS} batch={BATCH} negacyclic NTT+INTT, {BITS}-bit primes "
+                                   f"(BASELINE configs[1])",
+                       "bytes_resident": int(nbytes), "l2": "input (1 GiB) larger than L2, no flush needed",
+                       "partition": "batch axis, one batch per GPU, no collective",
+                       "chunk_limb_polys": args.chunk},
+            "clocks": clocks,
+            "e2e": {"value": world * LIMB_POLYS / e2e_s, "unit": "limb-polys/s",
+                    "h2d_bytes_per_step": 2 * nbytes, "d2h_bytes_per_step": 2 * nbytes,
+                    "ms_per_step": e2e_s * 1e3,
+                    "path": "mfhe_ntt_forward_host + mfhe_ntt_inverse_host on pinned host memory"},
+            "gpu_launches": 4 * args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "slower of forward (ntt_cols_kernel+ntt_rows_fwd_kernel) and inverse "
+                                   "(ntt_rows_inv_kernel+ntt_cols_kernel) transform; algorithmic bytes = "
+                                   "16*N per limb-poly per transform",
+                         "ms_forward": t_fwd * 1e3, "ms_inverse": t_inv * 1e3,
+                         "pair_frac": (2 * algo / (t_fwd + t_inv) / 1e9) / peak},
+        }
+        if not args.no_cpu:
+            n_lp, times, cores = cpu_sample(2 * LIMBS, 3)
+            line["cpu_baseline"] = {"value": n_lp / min(times), "unit": "limb-polys/s", "cores": cores,
+                                    "kind": "port",
+                                    "sample": f"{n_lp} limb-polys (2 of {BATCH} polys x {LIMBS} limbs), NTT+INTT, best of 3"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

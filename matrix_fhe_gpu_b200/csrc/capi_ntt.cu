@@ -1,0 +1,213 @@
+// capi_ntt.cu -- C ABI (include/mfhe.h) for the NTT family: plans, transforms, pointwise ops.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/mfhe.h"
+#include "capi_common.h"
+#include "ntt_api.h"
+#include "numth_host.hpp"
+
+using namespace mfhe;
+
+namespace mfhe {
+thread_local std::string g_last_error;
+int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+int cuda_fail(cudaError_t e, const char* where) {
+    return fail(MFHE_ECUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+}  // namespace mfhe
+
+extern "C" const char* mfhe_last_error(void) { return g_last_error.c_str(); }
+extern "C" const char* mfhe_version(void) { return "mfhe-b200 0.1 (sm_100a)"; }
+
+struct mfhe_ntt_plan {
+    int logn = 0, L = 0, convention = 0;
+    std::vector<uint64_t> moduli, roots;
+    u64* d_moduli = nullptr;
+    tw_t *d_tw = nullptr, *d_itw = nullptr, *d_ninv = nullptr, *d_w1n = nullptr;
+    ulonglong2* d_mu = nullptr;                // [L] floor(2^128 / q) as {lo, hi} (Barrett)
+    std::vector<host::TwPair> h_tw, h_itw;     // kept for mfhe_ntt_plan_get_table
+    size_t chunk = 0;
+    uint64_t* d_stage = nullptr;               // staging for the *_host entry points
+    size_t stage_bytes = 0;
+    NttTables flat() const { return NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L}; }
+    SmallTables small() const {
+        return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention};
+    }
+};
+
+extern "C" void mfhe_ntt_plan_destroy(mfhe_ntt_plan* p) {
+    if (!p) return;
+    cudaFree(p->d_moduli); cudaFree(p->d_tw); cudaFree(p->d_itw);
+    cudaFree(p->d_ninv); cudaFree(p->d_w1n); cudaFree(p->d_stage); cudaFree(p->d_mu);
+    delete p;
+}
+
+extern "C" int mfhe_ntt_plan_create(int logn, int L, const uint64_t* moduli, int convention,
+                                    mfhe_ntt_plan** out) {
+    if (!out) return fail(MFHE_EINVAL, "plan_create: out is NULL");
+    *out = nullptr;
+    const bool small = logn >= 4 && logn <= 8, flat = logn >= 12 && logn <= 17;
+    if (!small && !flat) return fail(MFHE_EUNSUPPORTED, "plan_create: logn must be in 4..8 or 12..17");
+    if (L <= 0 || !moduli) return fail(MFHE_EINVAL, "plan_create: no moduli");
+    if (convention < 0 || convention > 2) return fail(MFHE_EINVAL, "plan_create: unknown convention");
+    if (convention != MFHE_NTT_PHANTOM_NEGACYCLIC && !small)
+        return fail(MFHE_EUNSUPPORTED, "plan_create: gl/cyclic conventions need logn <= 8");
+    mfhe_ntt_plan* p = new (std::nothrow) mfhe_ntt_plan;
+    if (!p) return fail(MFHE_ENOMEM, "plan_create: host allocation failed");
+    p->logn = logn; p->L = L; p->convention = convention;
+    p->moduli.assign(moduli, moduli + L);
+    const size_t n = (size_t)1 << logn;
+    p->h_tw.resize(n * L); p->h_itw.resize(n * L);
+    std::vector<host::TwPair> ninv(L), w1n(L), mu(L);
+    try {
+        for (int l = 0; l < L; ++l) {
+            const uint64_t q = moduli[l];
+            if (q >= (1ull << 60) || q < 3 || !(q & 1))
+                throw std::runtime_error("modulus must be odd and below 2^60");
+            uint64_t psi, M, c0;
+            if (convention == MFHE_NTT_PHANTOM_NEGACYCLIC) {
+                M = 2 * n; c0 = n; psi = host::min_primitive_root(M, q);
+            } else {
+                M = 4 * n; psi = host::gl_psi(q, (int)n);
+                c0 = convention == MFHE_NTT_GL_XN_MINUS_I ? n : 0;
+            }
+            if (!psi) throw std::runtime_error("modulus " + std::to_string(q) + " has no root of the required order");
+            p->roots.push_back(psi);
+            host::TreeTables t = host::build_tree_tables(logn, q, psi, M, c0);
+            std::memcpy(&p->h_tw[l * n], t.tw.data(), n * sizeof(host::TwPair));
+            std::memcpy(&p->h_itw[l * n], t.itw.data(), n * sizeof(host::TwPair));
+            ninv[l] = t.ninv; w1n[l] = t.w1n;
+            const unsigned __int128 m = ~(unsigned __int128)0 / q;   // floor(2^128/q), q odd
+            mu[l] = host::TwPair{(uint64_t)m, (uint64_t)(m >> 64)};
+        }
+    } catch (const std::exception& e) {
+        delete p;
+        return fail(MFHE_EINVAL, std::string("plan_create: ") + e.what());
+    }
+    cudaError_t e;
+#define UP(dst, src, bytes)                                                              \
+    if ((e = cudaMalloc((void**)&(dst), (bytes))) != cudaSuccess ||                       \
+        (e = cudaMemcpy((dst), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) { \
+        mfhe_ntt_plan_destroy(p); return cuda_fail(e, "plan_create upload"); }
+    UP(p->d_moduli, p->moduli.data(), L * sizeof(uint64_t));
+    UP(p->d_tw, p->h_tw.data(), n * L * sizeof(tw_t));
+    UP(p->d_itw, p->h_itw.data(), n * L * sizeof(tw_t));
+    UP(p->d_ninv, ninv.data(), L * sizeof(tw_t));
+    UP(p->d_w1n, w1n.data(), L * sizeof(tw_t));
+    UP(p->d_mu, mu.data(), L * sizeof(ulonglong2));
+#undef UP
+    *out = p;
+    return MFHE_OK;
+}
+
+extern "C" int mfhe_ntt_plan_logn(const mfhe_ntt_plan* p) { return p ? p->logn : MFHE_EINVAL; }
+extern "C" int mfhe_ntt_plan_limbs(const mfhe_ntt_plan* p) { return p ? p->L : MFHE_EINVAL; }
+extern "C" uint64_t mfhe_ntt_plan_root(const mfhe_ntt_plan* p, int limb) {
+    return (p && limb >= 0 && limb < p->L) ? p->roots[limb] : 0;
+}
+extern "C" int mfhe_ntt_plan_get_table(const mfhe_ntt_plan* p, int limb, int inverse, uint64_t* w,
+                                       uint64_t* ws) {
+    if (!p || limb < 0 || limb >= p->L || !w || !ws) return fail(MFHE_EINVAL, "get_table: bad argument");
+    const size_t n = (size_t)1 << p->logn;
+    const host::TwPair* t = (inverse ? p->h_itw.data() : p->h_tw.data()) + limb * n;
+    for (size_t i = 0; i < n; ++i) { w[i] = t[i].w; ws[i] = t[i].ws; }
+    return MFHE_OK;
+}
+extern "C" int mfhe_ntt_plan_set_chunk(mfhe_ntt_plan* p, size_t chunk) {
+    if (!p) return fail(MFHE_EINVAL, "set_chunk: plan is NULL");
+    p->chunk = chunk;
+    return MFHE_OK;
+}
+
+static int run(const mfhe_ntt_plan* p, bool fwd, uint64_t* d, size_t batch, int ls, int lc, void* stream) {
+    if (!p || (!d && batch)) return fail(MFHE_EINVAL, "ntt: NULL plan or data");
+    if (ls < 0 || lc <= 0 || ls + lc > p->L) return fail(MFHE_EINVAL, "ntt: limb window out of range");
+    if (batch == 0) return MFHE_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e;
+    if (p->logn <= 8) {
+        if (ls != 0 || lc != p->L) return fail(MFHE_EUNSUPPORTED, "ntt: limb windows need logn >= 12");
+        e = ntt_small_launch(fwd, (u64*)d, p->small(), p->L, batch, st);
+    } else {
+        e = ntt_flat_launch(fwd, (u64*)d, p->flat(), ls, lc, batch, p->chunk, st);
+    }
+    return e == cudaSuccess ? MFHE_OK : cuda_fail(e, fwd ? "ntt_forward" : "ntt_inverse");
+}
+
+extern "C" int mfhe_ntt_forward(const mfhe_ntt_plan* p, uint64_t* d, size_t batch, void* s) {
+    return run(p, true, d, batch, 0, p ? p->L : 0, s);
+}
+extern "C" int mfhe_ntt_inverse(const mfhe_ntt_plan* p, uint64_t* d, size_t batch, void* s) {
+    return run(p, false, d, batch, 0, p ? p->L : 0, s);
+}
+extern "C" int mfhe_ntt_forward_limbs(const mfhe_ntt_plan* p, uint64_t* d, size_t batch, int ls, int lc, void* s) {
+    return run(p, true, d, batch, ls, lc, s);
+}
+extern "C" int mfhe_ntt_inverse_limbs(const mfhe_ntt_plan* p, uint64_t* d, size_t batch, int ls, int lc, void* s) {
+    return run(p, false, d, batch, ls, lc, s);
+}
+
+static int run_host(mfhe_ntt_plan* p, bool fwd, uint64_t* h, size_t batch) {
+    if (!p || (!h && batch)) return fail(MFHE_EINVAL, "ntt_host: NULL plan or data");
+    if (batch == 0) return MFHE_OK;
+    const size_t bytes = (batch * p->L << p->logn) * sizeof(uint64_t);
+    cudaError_t e;
+    if (bytes > p->stage_bytes) {
+        cudaFree(p->d_stage); p->d_stage = nullptr; p->stage_bytes = 0;
+        if ((e = cudaMalloc((void**)&p->d_stage, bytes)) != cudaSuccess) return cuda_fail(e, "ntt_host staging");
+        p->stage_bytes = bytes;
+    }
+    if ((e = cudaMemcpyAsync(p->d_stage, h, bytes, cudaMemcpyHostToDevice, 0)) != cudaSuccess) return cuda_fail(e, "ntt_host H2D");
+    int rc = run(p, fwd, p->d_stage, batch, 0, p->L, nullptr);
+    if (rc) return rc;
+    if ((e = cudaMemcpyAsync(h, p->d_stage, bytes, cudaMemcpyDeviceToHost, 0)) != cudaSuccess) return cuda_fail(e, "ntt_host D2H");
+    if ((e = cudaStreamSynchronize(0)) != cudaSuccess) return cuda_fail(e, "ntt_host sync");
+    return MFHE_OK;
+}
+extern "C" int mfhe_ntt_forward_host(mfhe_ntt_plan* p, uint64_t* h, size_t batch) { return run_host(p, true, h, batch); }
+extern "C" int mfhe_ntt_inverse_host(mfhe_ntt_plan* p, uint64_t* h, size_t batch) { return run_host(p, false, h, batch); }
+
+// ---- pointwise ------------------------------------------------------------------------
+namespace {
+enum PwOp { kMul, kAdd, kSub };
+
+template <int OP>
+__global__ void __launch_bounds__(256)
+pointwise_kernel(const u64* __restrict__ a, const u64* __restrict__ b, u64* __restrict__ out,
+                 const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu, int logn, int L,
+                 size_t total) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const u64 q = moduli[(i >> logn) % L];
+        const u64 x = a[i], y = b[i];
+        u64 r;
+        if (OP == kAdd) r = csub(x + y, q);
+        else if (OP == kSub) r = csub(x + q - y, q);
+        else {
+            const ulonglong2 m = mu[(i >> logn) % L];
+            r = mul_barrett(x, y, q, m.x, m.y);
+        }
+        out[i] = r;
+    }
+}
+}  // namespace
+
+static int pointwise(const mfhe_ntt_plan* p, int op, const uint64_t* a, const uint64_t* b, uint64_t* o,
+                     size_t batch, void* stream) {
+    if (!p || !a || !b || !o) return fail(MFHE_EINVAL, "pointwise: NULL argument");
+    const size_t total = batch * p->L << p->logn;
+    if (!total) return MFHE_OK;
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, 148 * 16);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (op == kMul) pointwise_kernel<kMul><<<grid, 256, 0, st>>>((const u64*)a, (const u64*)b, (u64*)o, (const u64*)p->d_moduli, p->d_mu, p->logn, p->L, total);
+    else if (op == kAdd) pointwise_kernel<kAdd><<<grid, 256, 0, st>>>((const u64*)a, (const u64*)b, (u64*)o, (const u64*)p->d_moduli, p->d_mu, p->logn, p->L, total);
+    else pointwise_kernel<kSub><<<grid, 256, 0, st>>>((const u64*)a, (const u64*)b, (u64*)o, (const u64*)p->d_moduli, p->d_mu, p->logn, p->L, total);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "pointwise");
+}
+extern "C" int mfhe_poly_mul(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kMul, a, b, o, batch, s); }
+extern "C" int mfhe_poly_add(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kAdd, a, b, o, batch, s); }
+extern "C" int mfhe_poly_sub(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kSub, a, b, o, batch, s); }

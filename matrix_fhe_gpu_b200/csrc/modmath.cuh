@@ -1,0 +1,95 @@
+// modmath.cuh -- 64-bit modular arithmetic for the sm_100a kernels.
+//
+// Replaces the reference's device helpers:
+//   include/core/common.cuh:12-39      add_mod / sub_mod / mul_mod (u128 %) / pow_mod
+//   include/backend/phantom_math.cuh:9-28   compute_shoup / multiply_and_reduce_shoup
+//   ph/include/uintmodmath.cuh:18-21,160-231  csub_q, lazy Shoup, Barrett
+// All public results are canonical in [0, q); q < 2^60 (checked at plan creation)
+// which leaves four spare bits for lazy accumulation up to 16q.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mfhe {
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+// {w, floor(w * 2^64 / q)} -- one 16-byte twiddle entry, one LDG.128.
+typedef ulonglong2 tw_t;
+
+__device__ __forceinline__ u64 csub(u64 x, u64 m) {       // x in [0, 2m) -> [0, m)
+    u64 t = x - m;
+    return t < x ? t : x;                                 // unsigned min trick: wraps when x < m
+}
+
+// x * w mod q, lazily: any 64-bit x, result in [0, 2q).
+__device__ __forceinline__ u64 mul_shoup_lazy(u64 x, tw_t w, u64 q) {
+    u64 hi = __umul64hi(x, w.y);
+    return x * w.x - hi * q;
+}
+__device__ __forceinline__ u64 mul_shoup(u64 x, tw_t w, u64 q) {
+    return csub(mul_shoup_lazy(x, w, q), q);
+}
+
+// compile-time conditional-subtract chain: value known < B*q is brought below T*q.
+template <int B, int T>
+__device__ __forceinline__ void reduce_bound(u64& x, u64 q) {
+    if constexpr (B > 8 && T <= 8) x = csub(x, 8 * q);
+    if constexpr (B > 4 && T <= 4) x = csub(x, 4 * q);
+    if constexpr (B > 2 && T <= 2) x = csub(x, 2 * q);
+    if constexpr (B > 1 && T <= 1) x = csub(x, q);
+}
+
+// ---- lazy-bound schedule of the forward (Cooley-Tukey) network -------------
+// A CT butterfly  x' = x + w*y, y' = x + 2q - w*y  with w*y in [0,2q) raises the
+// bound of both outputs to bound(x) + 2 (in units of q) whatever y was, because
+// the Shoup product accepts any 64-bit y.  With q < 2^60 values may grow to 16q,
+// so x needs a conditional subtract only every fourth stage instead of every
+// stage (ph/include/butterfly.cuh:10-22 subtracts in every butterfly).
+constexpr int kFwdInBound = 2;                       // inputs may be in [0, 2q)
+__host__ __device__ constexpr int fwd_xtarget(int B, int s, int logn) {
+    if (s == logn - 1) return 2;                     // last stage: leave < 4q for the final csubs
+    return (B + 2 > 16) ? 8 : B;
+}
+__host__ __device__ constexpr int fwd_bound_before(int s, int logn) {
+    int B = kFwdInBound;
+    for (int i = 0; i < s; ++i) B = fwd_xtarget(B, i, logn) + 2;
+    return B;
+}
+
+// Forward butterfly at global stage S of a 2^LOGN transform.
+template <int LOGN, int S>
+__device__ __forceinline__ void ct_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
+    constexpr int B = fwd_bound_before(S, LOGN);
+    constexpr int T = fwd_xtarget(B, S, LOGN);
+    reduce_bound<B, (T < B ? T : B)>(x, q);
+    u64 t = mul_shoup_lazy(y, w, q);
+    y = x + q2 - t;
+    x = x + t;
+}
+
+// Inverse (Gentleman-Sande) butterfly; all values stay in [0, 2q).
+__device__ __forceinline__ void gs_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
+    u64 t = x + q2 - y;
+    x = csub(x + y, q2);
+    y = mul_shoup_lazy(t, w, q);
+}
+
+// generic (non-constant multiplicand) product, Barrett on the 128-bit product.
+// mu = floor(2^128 / q) as {lo, hi}; result canonical.
+__device__ __forceinline__ u64 mul_barrett(u64 a, u64 b, u64 q, u64 mu_lo, u64 mu_hi) {
+    u64 lo = a * b, hi = __umul64hi(a, b);
+    // q_hat = floor((hi:lo) * mu / 2^128), computed from the three high partial products
+    u64 t1 = __umul64hi(lo, mu_lo);
+    u64 m_lo = lo * mu_hi, m_hi = __umul64hi(lo, mu_hi);
+    u64 s = t1 + m_lo; u64 c = s < t1;
+    u64 n_lo = hi * mu_lo, n_hi = __umul64hi(hi, mu_lo);
+    u64 s2 = s + n_lo; c += s2 < s;
+    u64 qhat = hi * mu_hi + m_hi + n_hi + c;
+    u64 r = lo - qhat * q;
+    r = csub(r, 2 * q);
+    return csub(r, q);
+}
+
+}  // namespace mfhe

@@ -1,0 +1,180 @@
+// ntt_small.cu -- batched n-point transforms, n = 2^4..2^8, for the matrix pipeline's X axis.
+//
+// Replaces, with ONE launch for all batch_count*limbs limb-polys,
+//   src/core/ntt_core.cu:443-460  xy_ntt_forward/backward_phantom (a host loop of
+//       batch_count launches of ph/src/ntt/ntt_1d.cu:17-76 / :194-256), and
+//   src/core/ntt_core.cu:394-431, 462-481  custom_ntt_* / xy_ntt_*_gl (copy + twist +
+//       bit-reverse + log2(n) global-memory stages + scale, ~10 passes over the data).
+// A limb-poly is owned by n/8 lanes (8 lanes for n = 64, four limb-polys per warp); the
+// coefficients stay in registers across stages and cross lanes through a warp-private
+// swizzled shared tile; global traffic is one read and one write per coefficient.
+//
+// All three conventions run the same merged Cooley-Tukey / Gentleman-Sande network: a node
+// of the product tree X^m - c splits into X^(m/2) -+ sqrt(c) and the twiddle of the node is
+// sqrt(c).  Only the host-built table (root constant -1, i or 1) and the output order differ:
+//   kPhantomNegacyclic  X^n + 1, natural in -> bit-reversed out  (Phantom order)
+//   kGlXnMinusI         X^n - i, natural in -> natural out: A[k] = sum a_j psi^j w^(jk)
+//   kCyclicNatural      X^n - 1, natural in -> natural out (custom_ntt_forward alone)
+#include "ntt_api.h"
+
+namespace mfhe {
+
+constexpr int kSmallThreads = 256;
+
+template <int LOGN> __device__ __forceinline__ u32 bitrev_n(u32 x) { return __brev(x) >> (32 - LOGN); }
+
+template <int LOGN, bool NATURAL>
+__global__ void __launch_bounds__(kSmallThreads)
+ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
+    constexpr int N = 1 << LOGN, TPP = N / 8, PPB = kSmallThreads / TPP, STRIDE = N + 8;
+    __shared__ __align__(16) u64 sm_all[PPB * STRIDE];
+    const u32 u = threadIdx.x % TPP, pib = threadIdx.x / TPP;
+    const size_t lp = (size_t)blockIdx.x * PPB + pib;
+    if (lp >= limb_polys) return;                       // whole polys drop out together (TPP <= 32)
+    const u32 limb = lp % limbs;
+    const u64 q = T.moduli[limb], q2 = 2 * q;
+    const tw_t* tw = T.tw + ((size_t)limb << LOGN);
+    u64* g = data + (lp << LOGN);
+    u64* sm = sm_all + pib * STRIDE;
+    u64 v[8];
+
+    constexpr int P0 = LOGN - 3;
+    constexpr int P1 = P0 > 3 ? P0 - 3 : 0;
+    constexpr int P2 = P1 > 3 ? P1 - 3 : 0;
+    {
+        const u32 e0 = deposit3(u, P0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = g[e0 + (j << P0)];
+        fwd_pass<LOGN, P0, 7>(v, e0, tw, q, q2);
+        if constexpr (P0 > 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[swz(e0 + (j << P0))] = v[j];
+        }
+    }
+    if constexpr (P0 > 0) {
+        __syncwarp();
+        const u32 e1 = deposit3(u, P1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << P1))];
+        fwd_pass<LOGN, P1, (1 << (P0 - P1)) - 1>(v, e1, tw, q, q2);
+        if constexpr (P1 > 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << P1))] = v[j];
+            __syncwarp();
+            const u32 e2 = deposit3(u, P2);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << P2))];
+            fwd_pass<LOGN, P2, (1 << (P1 - P2)) - 1>(v, e2, tw, q, q2);
+        }
+    }
+    static_assert(P2 == 0, "n <= 256");
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v[j] = csub(v[j], q2); v[j] = csub(v[j], q); }
+    // the thread now holds positions 8u .. 8u+7 of the bit-reversed-order result
+    if constexpr (NATURAL) {
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sm[swz(bitrev_n<LOGN>(8 * u + j))] = v[j];
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(sm + swz(8 * u + 2 * k));
+            v[2 * k] = t.x; v[2 * k + 1] = t.y;
+        }
+    }
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(g + 8 * u), "l"(v[0]), "l"(v[1]), "l"(v[2]), "l"(v[3]) : "memory");
+    asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(g + 8 * u + 4), "l"(v[4]), "l"(v[5]), "l"(v[6]), "l"(v[7]) : "memory");
+}
+
+template <int LOGN, bool NATURAL>
+__global__ void __launch_bounds__(kSmallThreads)
+ntt_small_inv_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
+    constexpr int N = 1 << LOGN, TPP = N / 8, PPB = kSmallThreads / TPP, STRIDE = N + 8;
+    __shared__ __align__(16) u64 sm_all[PPB * STRIDE];
+    const u32 u = threadIdx.x % TPP, pib = threadIdx.x / TPP;
+    const size_t lp = (size_t)blockIdx.x * PPB + pib;
+    if (lp >= limb_polys) return;
+    const u32 limb = lp % limbs;
+    const u64 q = T.moduli[limb], q2 = 2 * q;
+    const tw_t* itw = T.itw + ((size_t)limb << LOGN);
+    const tw_t ninv = T.ninv[limb], w1n = T.w1n[limb];
+    u64* g = data + (lp << LOGN);
+    u64* sm = sm_all + pib * STRIDE;
+    u64 v[8];
+
+    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(g + 8 * u));
+    asm volatile("ld.global.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(v[4]), "=l"(v[5]), "=l"(v[6]), "=l"(v[7]) : "l"(g + 8 * u + 4));
+    if constexpr (NATURAL) {       // natural-order evaluations -> network (bit-reversed) positions
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sm[swz(bitrev_n<LOGN>(8 * u + j))] = v[j];
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(sm + swz(8 * u + 2 * k));
+            v[2 * k] = t.x; v[2 * k + 1] = t.y;
+        }
+        __syncwarp();
+    }
+    constexpr int PL = LOGN - 3;
+    constexpr int P1 = PL < 3 ? PL : 3;
+    constexpr int P2 = PL < 6 ? PL : 6;
+    inv_pass<LOGN, 0, 7>(v, 8 * u, itw, q, q2, ninv, w1n);
+    if constexpr (PL > 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sm[swz(8 * u + j)] = v[j];
+        __syncwarp();
+        const u32 e1 = deposit3(u, P1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << P1))];
+        inv_pass<LOGN, P1, 7 & ~((1 << (3 - P1)) - 1)>(v, e1, itw, q, q2, ninv, w1n);
+        if constexpr (PL > 3) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << P1))] = v[j];
+            __syncwarp();
+            const u32 e2 = deposit3(u, P2);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << P2))];
+            inv_pass<LOGN, P2, 7 & ~((1 << (P1 + 3 - P2)) - 1)>(v, e2, itw, q, q2, ninv, w1n);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[e2 + (j << P2)] = v[j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) g[e1 + (j << P1)] = v[j];
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[8 * u + j] = v[j];
+    }
+}
+
+template <int LOGN>
+static cudaError_t launch_small(bool fwd, bool natural, u64* data, const SmallTables& T, int limbs,
+                                size_t limb_polys, cudaStream_t st) {
+    constexpr int PPB = kSmallThreads / ((1 << LOGN) / 8);
+    const unsigned grid = (unsigned)((limb_polys + PPB - 1) / PPB);
+    if (fwd) {
+        if (natural) ntt_small_fwd_kernel<LOGN, true><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+        else         ntt_small_fwd_kernel<LOGN, false><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+    } else {
+        if (natural) ntt_small_inv_kernel<LOGN, true><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+        else         ntt_small_inv_kernel<LOGN, false><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t ntt_small_launch(bool forward, u64* data, const SmallTables& T, int limbs, size_t batch,
+                             cudaStream_t st) {
+    const size_t limb_polys = batch * (size_t)limbs;
+    if (limb_polys == 0) return cudaSuccess;
+    const bool natural = T.convention != kPhantomNegacyclic;
+    switch (T.logn) {
+        case 4: return launch_small<4>(forward, natural, data, T, limbs, limb_polys, st);
+        case 5: return launch_small<5>(forward, natural, data, T, limbs, limb_polys, st);
+        case 6: return launch_small<6>(forward, natural, data, T, limbs, limb_polys, st);
+        case 7: return launch_small<7>(forward, natural, data, T, limbs, limb_polys, st);
+        case 8: return launch_small<8>(forward, natural, data, T, limbs, limb_polys, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace mfhe
