@@ -93,6 +93,163 @@ int mfhe_poly_add(const mfhe_ntt_plan *plan, const uint64_t *d_a, const uint64_t
 int mfhe_poly_sub(const mfhe_ntt_plan *plan, const uint64_t *d_a, const uint64_t *d_b,
                   uint64_t *d_out, size_t batch, void *stream);
 
+
+/* ======================================================================== *
+ * Matrix pipeline (family B of SURVEY.md): the reference's native ring
+ * Z_Q[X,Y,W]/(X^n - i, Y^n - i, Phi_p(W)), p = 3 f.  Reference shape: n = 64,
+ * f = 257 (p = 771, phi = 512 lanes), L = 11, delta = 2^35 (include/core/config.h:7-44).
+ *
+ * Layouts of an RNS "poly set" of T = phi*L*n*n words (src/core/HE.cu:1330-1368):
+ *   MATRIX  [w][limb][y][x]            (ciphertexts, encoder output, samplers)
+ *   POLY    [(w*n + y)][limb][x]       (what the reference's W-CRT kernels emit)
+ * Complex buffers are interleaved (re, im) doubles == cuDoubleComplex.
+ * ======================================================================== */
+typedef struct mfhe_ctx mfhe_ctx;
+#define MFHE_LAYOUT_MATRIX 0
+#define MFHE_LAYOUT_POLY   1
+
+typedef struct mfhe_params {
+    int n;                   /* MATRIX_N, power of two in 8..256                                  */
+    int f;                   /* odd prime; p = 3 f, phi = 2 (f - 1).  Reference: 257               */
+    int num_limbs;           /* RNS_NUM_LIMBS                                                      */
+    const uint64_t *moduli;  /* each = 1 mod lcm(2n, p), < 2^59                                    */
+    double delta;            /* SCALING_FACTOR                                                     */
+    size_t arena_bytes;      /* device scratch reserved at creation; 0 = what the pipeline needs   */
+} mfhe_params;
+
+/* Replaces init_he_backend (src/core/HE.cu:318-408): W-CRT / W-DFT tables, XY Vandermonde,
+ * CRT constants, n-point Phantom NTT tables, scratch arena -- everything the hot path needs, so
+ * that no later call allocates. */
+int mfhe_ctx_create(const mfhe_params *params, mfhe_ctx **out);
+void mfhe_ctx_destroy(mfhe_ctx *ctx);
+/* {n, f, p, phi, L, big_words} */
+int mfhe_ctx_info(const mfhe_ctx *ctx, int out[6]);
+/* copy_device_moduli (src/core/HE.cu:410-422): host out[count] */
+int mfhe_ctx_get_moduli(const mfhe_ctx *ctx, uint64_t *h_out, int count);
+uint64_t mfhe_ctx_eta(const mfhe_ctx *ctx, int limb);          /* h_find_eta, HE.cu:119-133 */
+/* host copy of the reference's device tables d_wntt_powers / d_wntt_inv_powers for one limb:
+ * out[w*phi + r] = V[w][r]  (inverse: V^-1[r][w]), HE.cu:258-266.  Parity aid. */
+int mfhe_ctx_get_wcrt_table(const mfhe_ctx *ctx, int limb, int inverse, uint64_t *h_out);
+/* CRT constants as the reference uploads them (encoder.cu:341-421): which = 0 Q[W], 1 Q/2[W],
+ * 2 M[L][W], 3 inv[L] */
+int mfhe_ctx_get_crt(const mfhe_ctx *ctx, int which, uint64_t *h_out);
+/* the n-point X-axis plan (Phantom negacyclic) owned by the context: get_xy_ntt_table, HE.cu:429-435 */
+const mfhe_ntt_plan *mfhe_ctx_xy_plan(const mfhe_ctx *ctx);
+
+/* ---- W-CRT: wntt_forward_matrix / wntt_inverse_matrix (HE.cu:437-452, 716-781) with explicit
+ * layouts (reference: forward MATRIX -> POLY, inverse POLY -> MATRIX); out must not alias in. */
+int mfhe_wcrt_forward(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, int in_layout, int out_layout, void *stream);
+int mfhe_wcrt_inverse(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, int in_layout, int out_layout, void *stream);
+/* wntt_forward_vector_kernel (HE.cu:1245-1270): [w][limb][x] */
+int mfhe_wcrt_forward_vector(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, void *stream);
+/* wntt_forward_centered / wntt_inverse_centered (HE.cu:454-470, 1029-1114): int64 [w][y][x] */
+int mfhe_wcrt_forward_centered(mfhe_ctx *ctx, const int64_t *d_in, int64_t *d_out, void *stream);
+int mfhe_wcrt_inverse_centered(mfhe_ctx *ctx, const int64_t *d_in, int64_t *d_out, void *stream);
+/* matrix_to_poly_kernel / poly_to_matrix_kernel (HE.cu:1330-1368, batched_encoder.cu:83-102) */
+int mfhe_layout_convert(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, int in_layout, int out_layout, void *stream);
+
+/* ---- complex W-DFT (HE.cu:472-502, 1116-1202; batched_encoder.cu:104-123): [phi][n*n] ------ */
+int mfhe_wdft_forward_complex(mfhe_ctx *ctx, const double *d_in, double *d_out, void *stream);
+int mfhe_wdft_inverse_complex(mfhe_ctx *ctx, const double *d_in, double *d_out, void *stream);
+int mfhe_wdft_forward_centered_pair(mfhe_ctx *ctx, const int64_t *d_re, const int64_t *d_im,
+                                    double *d_out_re, double *d_out_im, void *stream);
+int mfhe_wdft_inverse_pair(mfhe_ctx *ctx, const double *d_re, const double *d_im,
+                           double *d_out_re, double *d_out_im, void *stream);
+
+/* ---- XY canonical embedding, quantise, CRT (src/core/encoder.cu) ------------------------------ */
+/* Encoder::idft2 = Vinv M Vinv^T (encoder.cu:460-467) / decode_from_eval_complex = V E V^T
+ * (encoder.cu:492-501) for `lanes` n x n complex matrices in one launch */
+int mfhe_xy_idft2(mfhe_ctx *ctx, const double *d_in, double *d_out, int lanes, void *stream);
+int mfhe_xy_dft2(mfhe_ctx *ctx, const double *d_in, double *d_out, int lanes, void *stream);
+/* mat_mul_kernel_complex (encoder.cu:318-326): C = A B, n x n complex */
+int mfhe_matmul_complex(const double *d_A, const double *d_B, double *d_C, int n, void *stream);
+/* quantize_coeff_to_rns_kernel (batched_encoder.cu:125-152; lanes = phi) and quantize_soa_kernel
+ * (encoder.cu:36-50; lanes = 1): llround(z*delta) mod q_l -> [lane][limb][n*n] */
+int mfhe_quantize(mfhe_ctx *ctx, const double *d_in, uint64_t *d_re, uint64_t *d_im, int lanes, void *stream);
+/* crt_compose_centerlift_big (encoder.cu:191-245): in [lane][limbs][n2] -> mag [lane][n2][big_words],
+ * neg [lane][n2]; lanes > 1 replaces the reference's per-lane host loop (HE.cu:1653-1668) */
+int mfhe_crt_compose_big(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_mag, uint8_t *d_neg,
+                         int n2, int limbs, int lanes, void *stream);
+/* crt_compose_centerlift_kernel (encoder.cu:152-189; keeps the low word like the reference) */
+int mfhe_crt_compose_i64(mfhe_ctx *ctx, const uint64_t *d_in, int64_t *d_out, int n2, int limbs, void *stream);
+/* dequantize_exact_kernel (encoder.cu:112-150) */
+int mfhe_dequantize_exact(mfhe_ctx *ctx, const uint64_t *d_re, const uint64_t *d_im, double *d_out,
+                          int n2, int limbs, void *stream);
+/* compose_big_pair_to_complex_by_delta_kernel (HE.cu:1007-1027) */
+int mfhe_big_pair_to_complex(mfhe_ctx *ctx, const uint64_t *d_re_mag, const uint8_t *d_re_neg,
+                             const uint64_t *d_im_mag, const uint8_t *d_im_neg, double *d_out,
+                             size_t total, void *stream);
+/* BatchedEncoder::encode_to_wntt_eval (batched_encoder.cu:161-228): msg [phi][n*n] complex ->
+ * out_re, out_im MATRIX layout */
+int mfhe_encode(mfhe_ctx *ctx, const double *d_msg, uint64_t *d_out_re, uint64_t *d_out_im, void *stream);
+/* Encoder::encode (encoder.cu:446-456), one lane -> [limb][n*n] */
+int mfhe_encode_lane(mfhe_ctx *ctx, const double *d_msg, uint64_t *d_re, uint64_t *d_im, void *stream);
+/* decode_eval_pair_to_complex (HE.cu:1619-1689): evals in `layout` -> out [phi][n*n] complex */
+int mfhe_decode_eval_pair(mfhe_ctx *ctx, const uint64_t *d_eval_re, const uint64_t *d_eval_im, int layout,
+                          double *d_out, void *stream);
+/* Encoder::decode_lane_from_rns_eval (encoder.cu:469-490) */
+int mfhe_decode_lane_from_rns_eval(mfhe_ctx *ctx, const uint64_t *d_re, const uint64_t *d_im, double *d_out, void *stream);
+
+/* ---- samplers, keys, encrypt / decrypt (src/core/HE.cu) ------------------------------------------ */
+/* uniform_random_kernel :564-578, gaussian_noise_kernel :590-627 (MATRIX, W-coeff),
+ * ternary_secret_kernel :690-713 ([w][limb][x]) */
+int mfhe_sample_uniform(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
+int mfhe_sample_gaussian(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
+int mfhe_sample_ternary(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
+/* generate_secret_key (HE.cu:1272-1307): d_sk [w][limb][x], W-eval + X-NTT (Phantom order) */
+int mfhe_keygen(mfhe_ctx *ctx, uint64_t *d_sk, void *stream);
+/* encrypt_pair (HE.cu:1455-1552).  d_ct_* hold [b | a], T words each, MATRIX layout. */
+int mfhe_encrypt_pair(mfhe_ctx *ctx, const uint64_t *d_m_re, const uint64_t *d_m_im, const uint64_t *d_sk,
+                      uint64_t *d_ct_re, uint64_t *d_ct_im, void *stream);
+/* the same with caller-supplied a (W-coeff, MATRIX) and errors (W-coeff, MATRIX): the
+ * parity-checked integer core */
+int mfhe_encrypt_pair_with(mfhe_ctx *ctx, const uint64_t *d_m_re, const uint64_t *d_m_im, const uint64_t *d_sk,
+                           const uint64_t *d_a_coeff, const uint64_t *d_e_re, const uint64_t *d_e_im,
+                           uint64_t *d_ct_re, uint64_t *d_ct_im, void *stream);
+/* encrypt (HE.cu:1370-1453) */
+int mfhe_encrypt(mfhe_ctx *ctx, const uint64_t *d_m, const uint64_t *d_sk, uint64_t *d_ct, void *stream);
+/* decrypt_to_eval (HE.cu:1553-1601; out_layout POLY) / decrypt_to_eval_matrix (:1603-1617; MATRIX) */
+int mfhe_decrypt_to_eval(mfhe_ctx *ctx, const uint64_t *d_ct, const uint64_t *d_sk, uint64_t *d_out,
+                         int out_layout, void *stream);
+/* decrypt_and_decode (HE.cu:1691-1708) */
+int mfhe_decrypt_decode(mfhe_ctx *ctx, const uint64_t *d_ct_re, const uint64_t *d_ct_im, const uint64_t *d_sk,
+                        double *d_out, void *stream);
+/* add_ciphertexts / multiply_ciphertexts_raw (HE.cu:631-669, 1710-1740).  reference_indexing != 0
+ * takes the modulus of flat word idx as limb (idx / n) % L exactly as the reference kernels do
+ * (they index MATRIX data with the POLY formula); 0 uses the MATRIX layout's true limb. */
+int mfhe_ct_add(mfhe_ctx *ctx, const uint64_t *d_ct1, const uint64_t *d_ct2, uint64_t *d_res,
+                int reference_indexing, void *stream);
+int mfhe_ct_mul_raw(mfhe_ctx *ctx, const uint64_t *d_ct1, const uint64_t *d_ct2, uint64_t *d_d0, uint64_t *d_d1,
+                    uint64_t *d_d2, int reference_indexing, void *stream);
+
+/* ---- trace step (src/core/trace.cu:30-161, batched_trace.cu:37-197): [batch][limb][n][n] -------- */
+int mfhe_trace_map(mfhe_ctx *ctx, const uint64_t *d_Br, const uint64_t *d_Bi, uint64_t *d_Bpr, uint64_t *d_Bpi,
+                   int batch, void *stream);
+int mfhe_trace_gemm(mfhe_ctx *ctx, const uint64_t *d_Ar, const uint64_t *d_Ai, const uint64_t *d_Bpr,
+                    const uint64_t *d_Bpi, uint64_t *d_Cr, uint64_t *d_Ci, int batch, void *stream);
+int mfhe_trace_rescale(mfhe_ctx *ctx, uint64_t *d_Cr, uint64_t *d_Ci, int batch, uint64_t inv0, uint64_t inv1,
+                       uint64_t inv2, void *stream);
+
+/* ---- GL permutation (src/core/ntt_core.cu:150-173, 433-441) --------------------------------------- */
+int mfhe_gl_perm_tables(int n, uint32_t *h_perm, uint32_t *h_inv_perm);
+int mfhe_apply_gl_perm(const uint64_t *d_in, uint64_t *d_out, int limbs, int batch_count, int n, int inverse, void *stream);
+
+/* ---- RNS base conversion (Phantom DBaseConverter::bConv_BEHZ, ph/src/rns_bconv.cu:212-229) -------- */
+typedef struct mfhe_bconv_plan mfhe_bconv_plan;
+int mfhe_bconv_plan_create(int l_in, const uint64_t *q_in, int l_out, const uint64_t *p_out, mfhe_bconv_plan **out);
+void mfhe_bconv_plan_destroy(mfhe_bconv_plan *plan);
+/* d_in [batch][l_in][N] -> d_out [batch][l_out][N] */
+int mfhe_bconv(const mfhe_bconv_plan *plan, const uint64_t *d_in, uint64_t *d_out, size_t N, size_t batch, void *stream);
+/* limb-sharded form: this rank holds input limbs [in_start, in_start+in_count); writes the partial
+ * sums mod p_j of ALL output limbs, each < p_j, to d_partial [batch][l_out][N]; summing the ranks'
+ * partials mod p_j (mfhe_bconv_reduce after an all-gather / reduce-scatter) equals mfhe_bconv. */
+int mfhe_bconv_partial(const mfhe_bconv_plan *plan, const uint64_t *d_in_local, int in_start, int in_count,
+                       uint64_t *d_partial, size_t N, size_t batch, void *stream);
+/* d_parts [nparts][batch][out_count][N] -> d_out [batch][out_count][N], output limbs
+ * [out_start, out_start+out_count) */
+int mfhe_bconv_reduce(const mfhe_bconv_plan *plan, const uint64_t *d_parts, int nparts, int out_start, int out_count,
+                      uint64_t *d_out, size_t N, size_t batch, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,168 @@
+// bconv.cu -- fast RNS base conversion, Phantom's DBaseConverter::bConv_BEHZ semantics
+// (ph/src/rns_bconv.cu:22-29 bconv_mult, :109-131 bconv_matmul, :212-229 driver):
+//     y_i   = x_i * (Q/q_i)^-1 mod q_i                      i over the input base
+//     out_j = ( sum_i y_i * (Q/q_i mod p_j) ) mod p_j       j over the output base
+// One kernel instead of two and no [L_in][N] temporary in HBM: a CTA owns 128 coefficients, builds
+// their y_i in shared memory, then every thread forms all L_out sums for its coefficient with a
+// 128-bit lazy accumulator and a single Barrett reduction each (the accumulation trick of
+// ph/include/rns_bconv.cuh:112-126).  The sharded form computes the partial sum over a window of
+// input limbs (already reduced mod p_j, so partials from several GPUs add without overflow) and
+// mfhe_bconv_reduce adds the partials: this is the only step of the whole path that needs a
+// collective.
+#include <algorithm>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/mfhe.h"
+#include "capi_common.h"
+#include "modmath.cuh"
+#include "numth_host.hpp"
+
+using namespace mfhe;
+
+struct mfhe_bconv_plan {
+    int l_in = 0, l_out = 0;
+    std::vector<uint64_t> q, p;
+    u64 *d_q = nullptr, *d_p = nullptr;
+    tw_t* d_qhat_inv = nullptr;        // [l_in] {(Q/q_i)^-1 mod q_i, shoup}
+    u64* d_qhat_mod_p = nullptr;       // [l_out][l_in]
+    ulonglong2* d_mu_p = nullptr;      // [l_out] floor(2^128 / p_j)
+};
+
+namespace {
+constexpr int BC = 128;    // coefficients per CTA
+
+__global__ void __launch_bounds__(BC)
+bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_in_total, int in_start, int in_count,
+             int l_out, const u64* __restrict__ q, const tw_t* __restrict__ qhat_inv, const u64* __restrict__ qhat_mod_p,
+             const u64* __restrict__ p, const ulonglong2* __restrict__ mu_p) {
+    extern __shared__ u64 sy[];        // [in_count][BC]
+    const size_t d = (size_t)blockIdx.x * BC + threadIdx.x;
+    const size_t b = blockIdx.y;
+    const bool live = d < N;
+    const u64* x = in + b * (size_t)in_count * N;
+    for (int i = 0; i < in_count; ++i) {
+        const int gi = in_start + i;
+        sy[i * BC + threadIdx.x] = live ? mul_shoup(x[(size_t)i * N + d], qhat_inv[gi], q[gi]) : 0;
+    }
+    // each thread reads back only its own column: no barrier needed
+    if (!live) return;
+    u64* o = out + b * (size_t)l_out * N;
+    for (int j = 0; j < l_out; ++j) {
+        u64 lo = 0, hi = 0;
+        const u64* w = qhat_mod_p + (size_t)j * l_in_total + in_start;
+        for (int i = 0; i < in_count; ++i) {
+            const u64 y = sy[i * BC + threadIdx.x], c = __ldg(w + i);
+            const u64 pl = y * c, ph = __umul64hi(y, c);
+            lo += pl; hi += ph + (lo < pl);
+        }
+        const ulonglong2 m = mu_p[j];
+        o[(size_t)j * N + d] = reduce128(lo, hi, p[j], m.x, m.y);
+    }
+}
+
+__global__ void bconv_reduce_kernel(const u64* __restrict__ parts, u64* __restrict__ out, size_t per_part, int nparts,
+                                    size_t N, int out_start, int out_count, const u64* __restrict__ p,
+                                    const ulonglong2* __restrict__ mu_p) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= per_part) return;
+    const int j = out_start + (int)((idx / N) % out_count);
+    u64 s = 0;
+    for (int k = 0; k < nparts; ++k) s += parts[(size_t)k * per_part + idx];      // nparts * p_j < 2^64
+    out[idx] = reduce64(s, p[j], mu_p[j].y);
+}
+}  // namespace
+
+extern "C" void mfhe_bconv_plan_destroy(mfhe_bconv_plan* b) {
+    if (!b) return;
+    cudaFree(b->d_q); cudaFree(b->d_p); cudaFree(b->d_qhat_inv); cudaFree(b->d_qhat_mod_p); cudaFree(b->d_mu_p);
+    delete b;
+}
+
+extern "C" int mfhe_bconv_plan_create(int l_in, const uint64_t* q_in, int l_out, const uint64_t* p_out, mfhe_bconv_plan** out) {
+    if (!out) return fail(MFHE_EINVAL, "bconv_plan_create: out is NULL");
+    *out = nullptr;
+    if (l_in < 1 || l_in > 128 || l_out < 1 || l_out > 128 || !q_in || !p_out) return fail(MFHE_EINVAL, "bconv_plan_create: bad sizes");
+    mfhe_bconv_plan* b = new (std::nothrow) mfhe_bconv_plan;
+    if (!b) return fail(MFHE_ENOMEM, "bconv_plan_create: host allocation failed");
+    b->l_in = l_in; b->l_out = l_out; b->q.assign(q_in, q_in + l_in); b->p.assign(p_out, p_out + l_out);
+    std::vector<host::TwPair> qi(l_in), mu(l_out);
+    std::vector<uint64_t> qp((size_t)l_in * l_out);
+    // lazy 128-bit accumulation needs l_in * q * p < 2^128
+    long double bound = (long double)l_in;
+    uint64_t qmax = 0, pmax = 0;
+    for (int i = 0; i < l_in; ++i) qmax = std::max(qmax, q_in[i]);
+    for (int j = 0; j < l_out; ++j) pmax = std::max(pmax, p_out[j]);
+    bound *= (long double)qmax * (long double)pmax;
+    if (qmax >= (1ull << 61) || pmax >= (1ull << 61) || bound >= 3.4028236692093846e38L) {
+        delete b; return fail(MFHE_EUNSUPPORTED, "bconv_plan_create: l_in * q * p must stay below 2^128 and moduli below 2^61");
+    }
+    for (int i = 0; i < l_in; ++i) {
+        const uint64_t q = q_in[i];
+        if (q < 3 || !(q & 1)) { delete b; return fail(MFHE_EINVAL, "bconv_plan_create: moduli must be odd"); }
+        uint64_t pr = 1;
+        for (int k = 0; k < l_in; ++k) if (k != i) pr = host::mulmod(pr, q_in[k] % q, q);
+        if (!pr) { delete b; return fail(MFHE_EINVAL, "bconv_plan_create: input moduli are not coprime"); }
+        const uint64_t inv = host::invmod(pr, q);
+        qi[i] = host::TwPair{inv, host::shoup(inv, q)};
+        for (int j = 0; j < l_out; ++j) {
+            uint64_t pj = 1;
+            for (int k = 0; k < l_in; ++k) if (k != i) pj = host::mulmod(pj, q_in[k] % p_out[j], p_out[j]);
+            qp[(size_t)j * l_in + i] = pj;
+        }
+    }
+    for (int j = 0; j < l_out; ++j) {
+        const unsigned __int128 m = ~(unsigned __int128)0 / p_out[j];
+        mu[j] = host::TwPair{(uint64_t)m, (uint64_t)(m >> 64)};
+    }
+    cudaError_t e;
+#define UP(dst, src, bytes)                                                                 \
+    if ((e = cudaMalloc((void**)&(dst), (bytes))) != cudaSuccess ||                          \
+        (e = cudaMemcpy((dst), (src), (bytes), cudaMemcpyHostToDevice)) != cudaSuccess) {    \
+        mfhe_bconv_plan_destroy(b); return cuda_fail(e, "bconv_plan_create upload"); }
+    UP(b->d_q, b->q.data(), (size_t)l_in * 8); UP(b->d_p, b->p.data(), (size_t)l_out * 8);
+    UP(b->d_qhat_inv, qi.data(), (size_t)l_in * 16); UP(b->d_qhat_mod_p, qp.data(), qp.size() * 8);
+    UP(b->d_mu_p, mu.data(), (size_t)l_out * 16);
+#undef UP
+    *out = b;
+    return MFHE_OK;
+}
+
+static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start, int in_count, uint64_t* out, size_t N,
+                     size_t batch, void* stream, const char* who) {
+    if (!b || !in || !out) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
+    if (in_start < 0 || in_count < 1 || in_start + in_count > b->l_in) return fail(MFHE_EINVAL, std::string(who) + ": limb window out of range");
+    if (!N || !batch) return MFHE_OK;
+    if (batch > 65535) return fail(MFHE_EINVAL, std::string(who) + ": batch too large");
+    const size_t smem = (size_t)in_count * BC * 8;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(bconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, who);
+        attr_set = true;
+    }
+    dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
+    bconv_kernel<<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out,
+                                                          b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
+}
+extern "C" int mfhe_bconv(const mfhe_bconv_plan* b, const uint64_t* in, uint64_t* out, size_t N, size_t batch, void* s) {
+    return bconv_run(b, in, 0, b ? b->l_in : 0, out, N, batch, s, "bconv");
+}
+extern "C" int mfhe_bconv_partial(const mfhe_bconv_plan* b, const uint64_t* in, int in_start, int in_count, uint64_t* out,
+                                  size_t N, size_t batch, void* s) {
+    return bconv_run(b, in, in_start, in_count, out, N, batch, s, "bconv_partial");
+}
+extern "C" int mfhe_bconv_reduce(const mfhe_bconv_plan* b, const uint64_t* parts, int nparts, int out_start, int out_count,
+                                 uint64_t* out, size_t N, size_t batch, void* s) {
+    if (!b || !parts || !out || nparts < 1 || nparts > 8 || out_start < 0 || out_count < 1 || out_start + out_count > b->l_out)
+        return fail(MFHE_EINVAL, "bconv_reduce: bad argument");
+    const size_t per = batch * (size_t)out_count * N;
+    if (!per) return MFHE_OK;
+    bconv_reduce_kernel<<<(unsigned)((per + 255) / 256), 256, 0, (cudaStream_t)s>>>((const u64*)parts, (u64*)out, per, nparts, N,
+                                                                                  out_start, out_count, b->d_p, b->d_mu_p);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "bconv_reduce");
+}

@@ -9,6 +9,7 @@
 #include "capi_common.h"
 #include "ntt_api.h"
 #include "numth_host.hpp"
+#include "plan.h"
 
 using namespace mfhe;
 
@@ -22,22 +23,6 @@ int cuda_fail(cudaError_t e, const char* where) {
 
 extern "C" const char* mfhe_last_error(void) { return g_last_error.c_str(); }
 extern "C" const char* mfhe_version(void) { return "mfhe-b200 0.1 (sm_100a)"; }
-
-struct mfhe_ntt_plan {
-    int logn = 0, L = 0, convention = 0;
-    std::vector<uint64_t> moduli, roots;
-    u64* d_moduli = nullptr;
-    tw_t *d_tw = nullptr, *d_itw = nullptr, *d_ninv = nullptr, *d_w1n = nullptr;
-    ulonglong2* d_mu = nullptr;                // [L] floor(2^128 / q) as {lo, hi} (Barrett)
-    std::vector<host::TwPair> h_tw, h_itw;     // kept for mfhe_ntt_plan_get_table
-    size_t chunk = 0;
-    uint64_t* d_stage = nullptr;               // staging for the *_host entry points
-    size_t stage_bytes = 0;
-    NttTables flat() const { return NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L}; }
-    SmallTables small() const {
-        return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention};
-    }
-};
 
 extern "C" void mfhe_ntt_plan_destroy(mfhe_ntt_plan* p) {
     if (!p) return;

@@ -1,0 +1,117 @@
+// ctx.h -- internal definition of mfhe_ctx (the matrix pipeline's context) and the launchers
+// the C-ABI layer (capi_scheme.cu) calls.  Everything here is device-pointer plumbing.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+#include <cuda_runtime.h>
+
+#include "../../include/mfhe.h"
+#include "modmath.cuh"
+
+struct mfhe_ctx {
+    int n = 0, logn = 0, f = 0, p = 0, phi = 0, L = 0, W = 0;     // W = 64-bit words of Q
+    double delta = 0;
+    std::vector<uint64_t> moduli, eta;
+    std::vector<uint16_t> wexp;
+    std::vector<uint64_t> hV, hVinv;          // [L][phi][phi]: V[w][r] and V^-1[r][w] (row-major)
+    std::vector<uint64_t> hQ, hQhalf, hM, hInv;
+    // device tables
+    mfhe::u64* d_moduli = nullptr;            // [L]
+    ulonglong2* d_mu = nullptr;               // [L] floor(2^128/q) {lo, hi}
+    mfhe::u64* d_wtab_fwd = nullptr;          // [L][i = W-coeff r][o = lane w]   (transposed for the GEMM)
+    mfhe::u64* d_wtab_inv = nullptr;          // [L][i = lane w][o = W-coeff r]
+    int wsplit = 0;                           // 1: tables stored as {lo26, hi} pairs (all q < 2^52)
+    double2* d_wdft_fwd = nullptr;            // [i = r][o = w]
+    double2* d_wdft_inv = nullptr;            // [i = w][o = r]
+    double2 *d_xyV = nullptr, *d_xyVT = nullptr, *d_xyVinv = nullptr, *d_xyVinvT = nullptr;   // [n][n]
+    mfhe::u64 *d_crt_Q = nullptr, *d_crt_Qhalf = nullptr, *d_crt_M = nullptr, *d_crt_inv = nullptr;
+    mfhe_ntt_plan* xy_plan = nullptr;
+    char* arena = nullptr;
+    size_t arena_bytes = 0, arena_used = 0;
+
+    size_t n2() const { return (size_t)n * n; }
+    size_t T() const { return (size_t)phi * L * n * n; }
+    // bump allocator over the arena reserved at creation (reset at the start of every API call)
+    void arena_reset() { arena_used = 0; }
+    void* take(size_t bytes) {
+        size_t off = (arena_used + 255) & ~(size_t)255;
+        if (off + bytes > arena_bytes) return nullptr;
+        arena_used = off + bytes;
+        return arena + off;
+    }
+};
+
+namespace mfhe {
+
+// ---- W-CRT as a per-limb modular GEMM  out[o][col] = sum_i tab[limb][i][o] * in[i][col] ----------
+enum WcrtSource { kSrcMem = 0, kSrcI64 = 1, kSrcQuantRe = 2, kSrcQuantIm = 3, kSrcUniform = 4, kSrcGauss = 5 };
+struct WcrtArgs {
+    const void* in = nullptr;      // u64 / int64 / double2 depending on the source
+    u64* out = nullptr;
+    u64* out2 = nullptr;           // optional duplicate of the output (encrypt_pair stores a twice)
+    const u64* tab = nullptr;      // [limbs][phi][phi]
+    const u64* moduli = nullptr;
+    const ulonglong2* mu = nullptr;
+    int n = 0, cols = 0;           // cols = n*n (matrix form) or n (vector form); rows of n along x
+    int limbs = 0, phi = 0;
+    int limb0 = 0;                 // first limb of `tab`/`moduli` used (kSrcI64 inverse: limb 0 only)
+    int in_layout = 0, out_layout = 0;
+    int source = kSrcMem;
+    int split = 0;
+    double delta = 0;
+};
+cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st);
+
+// ---- fp64 complex kernels (fp64ops.cu) --------------------------------------------------------------
+// out[o][col] = sum_i tab[i][o] * in[i][col], phi x phi table, cols columns
+cudaError_t wdft_launch(const double2* tab, const double2* in, double2* out, int phi, int cols, cudaStream_t st);
+// same on split planes: in = (re, im) of type double (pair = 0) or int64 (pair = 1)
+cudaError_t wdft_pair_launch(const double2* tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
+                             int phi, int cols, int int_input, cudaStream_t st);
+// out = A * in * B per lane (A, B n x n), lanes matrices
+cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,
+                               cudaStream_t st);
+cudaError_t matmul_complex_launch(const double2* A, const double2* B, double2* C, int n, cudaStream_t st);
+cudaError_t quantize_launch(const double2* in, u64* re, u64* im, const u64* moduli, const ulonglong2* mu, int n2,
+                            int limbs, int lanes, double delta, cudaStream_t st);
+
+// ---- CRT compose (crt.cu) ----------------------------------------------------------------------------
+struct CrtDev { const u64 *Q, *Qhalf, *M, *inv, *moduli; const ulonglong2* mu; int W; };
+cudaError_t crt_compose_big_launch(const CrtDev& c, const u64* in, u64* mag, uint8_t* neg, int n2, int limbs, int lanes,
+                                   int lane_stride_limbs, cudaStream_t st);
+cudaError_t crt_compose_i64_launch(const CrtDev& c, const u64* in, long long* out, int n2, int limbs, int lanes,
+                                   int saturate, cudaStream_t st);
+cudaError_t center_i64_launch(const u64* in, long long* out, u64 q, size_t total, cudaStream_t st);
+// in_re / in_im [lane][limbs][n2] -> complex out [lane][n2] = centred value / delta
+cudaError_t crt_to_complex_launch(const CrtDev& c, const u64* in_re, const u64* in_im, double2* out, int n2, int limbs,
+                                  int lanes, double delta, cudaStream_t st);
+cudaError_t big_pair_to_complex_launch(const u64* re_mag, const uint8_t* re_neg, const u64* im_mag, const uint8_t* im_neg,
+                                       double2* out, size_t total, int W, double delta, cudaStream_t st);
+
+// ---- scheme kernels (scheme.cu) ------------------------------------------------------------------------
+struct RowArgs {                 // one launch over all phi*L*n rows of n coefficients
+    const u64 *a = nullptr, *s = nullptr;          // a rows (layout a_layout), key [w][l][x]
+    const u64 *m0 = nullptr, *e0 = nullptr; u64* o0 = nullptr;   // out0 = m0 -/+ t + e0
+    const u64 *m1 = nullptr, *e1 = nullptr; u64* o1 = nullptr;   // optional second component
+    int a_layout = 0, m_layout = 0, e_layout = 0, o_layout = 0;
+    int subtract = 1;            // 1: out = m - t + e (encrypt), 0: out = m + t (decrypt; e ignored)
+    int n = 0, limbs = 0, phi = 0;
+};
+struct SmallTables;
+cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulonglong2* mu, cudaStream_t st);
+cudaError_t sample_launch(int kind, u64* out, const u64* moduli, int n, int limbs, int phi, cudaStream_t st);
+cudaError_t layout_launch(const u64* in, u64* out, int n, int limbs, int phi, int in_layout, int out_layout, cudaStream_t st);
+cudaError_t ct_add_launch(const u64* c1, const u64* c2, u64* res, const u64* moduli, size_t T, int n, int limbs,
+                          int ref_index, cudaStream_t st);
+cudaError_t ct_mul_launch(const u64* c1, const u64* c2, u64* d0, u64* d1, u64* d2, const u64* moduli, const ulonglong2* mu,
+                          size_t T, int n, int limbs, int ref_index, cudaStream_t st);
+cudaError_t trace_map_launch(const u64* Br, const u64* Bi, u64* Bpr, u64* Bpi, const u64* moduli, int n, int limbs,
+                             int batch, cudaStream_t st);
+cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
+                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st);
+cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
+                                 u64 inv0, u64 inv1, u64 inv2, cudaStream_t st);
+cudaError_t gl_perm_launch(const u64* in, u64* out, const uint32_t* perm, int limbs, int batch, int n, cudaStream_t st);
+
+}  // namespace mfhe

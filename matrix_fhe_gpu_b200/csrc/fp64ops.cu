@@ -1,0 +1,184 @@
+// fp64ops.cu -- the floating-point half of encode / decode.
+//
+//   wdft_*        complex W-(I)DFT as one tiled complex GEMM over all n*n columns
+//                 (replaces HE.cu:1116-1202 and batched_encoder.cu:104-123: one thread per output,
+//                 table re-read from global memory per thread)
+//   xy_sandwich   out = A * M * B for all lanes in ONE launch, M staged in shared memory
+//                 (replaces the 512-iteration host loops of cudaMalloc + 2 launches of
+//                 mat_mul_kernel_complex<<<(4,4),(16,16)>>> + cudaFree: encoder.cu:460-467, 492-501,
+//                 batched_encoder.cu:192-196, HE.cu:1676-1679)
+//   quantize      llround(z * delta) mod q_l (batched_encoder.cu:125-152, encoder.cu:36-50)
+// fp64 results agree with the reference within summation-order round-off (tolerance-checked).
+#include "ctx.h"
+
+namespace mfhe {
+
+constexpr int DTO = 64, DTC = 64, DTK = 8, DTHREADS = 256;
+
+// IN: 0 interleaved complex, 1 two double planes, 2 two int64 planes.  OUT: 0 interleaved, 1 planes.
+template <int IN, int OUT>
+__global__ void __launch_bounds__(DTHREADS)
+wdft_gemm_kernel(const double2* __restrict__ tab, const void* __restrict__ in0, const void* __restrict__ in1,
+                 void* __restrict__ out0, void* __restrict__ out1, int phi, int cols) {
+    __shared__ __align__(16) double2 sTab[2][DTK][DTO];
+    __shared__ __align__(16) double2 sIn[2][DTK][DTC];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int o0 = blockIdx.y * DTO, c0 = blockIdx.x * DTC;
+    // staging: 8 rows x 64 entries = 512 entries per tile, 2 per thread
+    const int lk = t >> 5, lg = (t & 31) << 1;
+    double2 rt[2], ri[2];
+    auto fetch = [&](int k0) {
+        const int i = k0 + lk;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            rt[j] = (i < phi && o0 + lg + j < phi) ? __ldg(tab + (size_t)i * phi + o0 + lg + j) : make_double2(0, 0);
+            const int c = c0 + lg + j;
+            if (i < phi && c < cols) {
+                const size_t off = (size_t)i * cols + c;
+                if (IN == 0) ri[j] = __ldg((const double2*)in0 + off);
+                else if (IN == 1) ri[j] = make_double2(((const double*)in0)[off], ((const double*)in1)[off]);
+                else ri[j] = make_double2((double)((const long long*)in0)[off], (double)((const long long*)in1)[off]);
+            } else ri[j] = make_double2(0, 0);
+        }
+    };
+    auto stash = [&](int buf) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { sTab[buf][lk][lg + j] = rt[j]; sIn[buf][lk][lg + j] = ri[j]; }
+    };
+    double ar[4][4], ai[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ar[i][j] = ai[i][j] = 0.0;
+    fetch(0); stash(0);
+    __syncthreads();
+    const int ktiles = (phi + DTK - 1) / DTK;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * DTK);
+#pragma unroll
+        for (int k = 0; k < DTK; ++k) {
+            double2 a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = sTab[buf][k][ty * 4 + i]; b[i] = sIn[buf][k][tx * 4 + i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    ar[i][j] = fma(a[i].x, b[j].x, ar[i][j]); ar[i][j] = fma(-a[i].y, b[j].y, ar[i][j]);
+                    ai[i][j] = fma(a[i].x, b[j].y, ai[i][j]); ai[i][j] = fma(a[i].y, b[j].x, ai[i][j]);
+                }
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int o = o0 + ty * 4 + i;
+        if (o >= phi) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = c0 + tx * 4 + j;
+            if (c >= cols) continue;
+            const size_t off = (size_t)o * cols + c;
+            if (OUT == 0) ((double2*)out0)[off] = make_double2(ar[i][j], ai[i][j]);
+            else { ((double*)out0)[off] = ar[i][j]; ((double*)out1)[off] = ai[i][j]; }
+        }
+    }
+}
+
+cudaError_t wdft_launch(const double2* tab, const double2* in, double2* out, int phi, int cols, cudaStream_t st) {
+    dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
+    wdft_gemm_kernel<0, 0><<<grid, DTHREADS, 0, st>>>(tab, in, nullptr, out, nullptr, phi, cols);
+    return cudaGetLastError();
+}
+cudaError_t wdft_pair_launch(const double2* tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
+                             int phi, int cols, int int_input, cudaStream_t st) {
+    dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
+    if (int_input) wdft_gemm_kernel<2, 1><<<grid, DTHREADS, 0, st>>>(tab, in_re, in_im, out_re, out_im, phi, cols);
+    else           wdft_gemm_kernel<1, 1><<<grid, DTHREADS, 0, st>>>(tab, in_re, in_im, out_re, out_im, phi, cols);
+    return cudaGetLastError();
+}
+
+// ---- out = A * M * B per lane ---------------------------------------------------------------------
+__device__ __forceinline__ double2 cfma(double2 a, double2 b, double2 c) {
+    c.x = fma(a.x, b.x, c.x); c.x = fma(-a.y, b.y, c.x);
+    c.y = fma(a.x, b.y, c.y); c.y = fma(a.y, b.x, c.y);
+    return c;
+}
+__global__ void __launch_bounds__(256)
+xy_sandwich_kernel(const double2* __restrict__ A, const double2* __restrict__ B, const double2* __restrict__ in,
+                   double2* __restrict__ out, int n) {
+    extern __shared__ __align__(16) double2 sm_xy[];
+    double2* sM = sm_xy;                 // [n][n] the lane's matrix
+    double2* sT = sm_xy + (size_t)n * n; // [n][n] A * M
+    const size_t nn = (size_t)n * n;
+    const double2* M = in + (size_t)blockIdx.x * nn;
+    for (size_t i = threadIdx.x; i < nn; i += blockDim.x) sM[i] = M[i];
+    __syncthreads();
+    for (size_t idx = threadIdx.x; idx < nn; idx += blockDim.x) {
+        const int r = (int)(idx / n), c = (int)(idx % n);
+        double2 acc = make_double2(0, 0);
+        for (int k = 0; k < n; ++k) acc = cfma(__ldg(A + (size_t)r * n + k), sM[(size_t)k * n + c], acc);
+        sT[idx] = acc;
+    }
+    __syncthreads();
+    double2* O = out + (size_t)blockIdx.x * nn;
+    for (size_t idx = threadIdx.x; idx < nn; idx += blockDim.x) {
+        const int r = (int)(idx / n), c = (int)(idx % n);
+        double2 acc = make_double2(0, 0);
+        for (int k = 0; k < n; ++k) acc = cfma(sT[(size_t)r * n + k], __ldg(B + (size_t)k * n + c), acc);
+        O[idx] = acc;
+    }
+}
+cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,
+                               cudaStream_t st) {
+    const size_t smem = 2 * (size_t)n * n * sizeof(double2);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(xy_sandwich_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    xy_sandwich_kernel<<<lanes, 256, smem, st>>>(A, B, in, out, n);
+    return cudaGetLastError();
+}
+
+__global__ void matmul_complex_kernel(const double2* A, const double2* B, double2* C, int n) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * n) return;
+    const int r = idx / n, c = idx % n;
+    double2 acc = make_double2(0, 0);
+    for (int k = 0; k < n; ++k) acc = cfma(A[(size_t)r * n + k], B[(size_t)k * n + c], acc);
+    C[idx] = acc;
+}
+cudaError_t matmul_complex_launch(const double2* A, const double2* B, double2* C, int n, cudaStream_t st) {
+    matmul_complex_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(A, B, C, n);
+    return cudaGetLastError();
+}
+
+// ---- quantise ----------------------------------------------------------------------------------------
+__global__ void quantize_kernel(const double2* __restrict__ in, u64* __restrict__ re, u64* __restrict__ im,
+                                const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu, int n2, int limbs,
+                                size_t total, double delta) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t lane = idx / n2, pos = idx % n2;
+    const double2 z = in[idx];
+    const long long xr = llround(z.x * delta), xi = llround(z.y * delta);
+    for (int l = 0; l < limbs; ++l) {
+        const u64 q = moduli[l], mh = mu[l].y;
+        const size_t o = (lane * limbs + l) * n2 + pos;
+        re[o] = signed_mod(xr, q, mh);
+        im[o] = signed_mod(xi, q, mh);
+    }
+}
+cudaError_t quantize_launch(const double2* in, u64* re, u64* im, const u64* moduli, const ulonglong2* mu, int n2,
+                            int limbs, int lanes, double delta, cudaStream_t st) {
+    const size_t total = (size_t)lanes * n2;
+    quantize_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, re, im, moduli, mu, n2, limbs, total, delta);
+    return cudaGetLastError();
+}
+
+}  // namespace mfhe

@@ -93,3 +93,38 @@ __device__ __forceinline__ u64 mul_barrett(u64 a, u64 b, u64 q, u64 mu_lo, u64 m
 }
 
 }  // namespace mfhe
+
+// ---- helpers added for the matrix pipeline --------------------------------------------------
+namespace mfhe {
+
+// (hi:lo) mod q for any 128-bit value, mu = floor(2^128 / q) as {lo, hi}; canonical result.
+__device__ __forceinline__ u64 reduce128(u64 lo, u64 hi, u64 q, u64 mu_lo, u64 mu_hi) {
+    u64 t1 = __umul64hi(lo, mu_lo);
+    u64 m_lo = lo * mu_hi, m_hi = __umul64hi(lo, mu_hi);
+    u64 s = t1 + m_lo; u64 c = s < t1;
+    u64 n_lo = hi * mu_lo, n_hi = __umul64hi(hi, mu_lo);
+    u64 s2 = s + n_lo; c += s2 < s;
+    u64 qhat = hi * mu_hi + m_hi + n_hi + c;
+    u64 r = lo - qhat * q;
+    r = csub(r, 2 * q);
+    return csub(r, q);
+}
+__device__ __forceinline__ u64 add_mod(u64 a, u64 b, u64 q) { return csub(a + b, q); }
+__device__ __forceinline__ u64 sub_mod(u64 a, u64 b, u64 q) { return csub(a + q - b, q); }
+__device__ __forceinline__ u64 neg_mod(u64 a, u64 q) { return a ? q - a : 0; }
+// x mod q for any 64-bit x
+__device__ __forceinline__ u64 reduce64(u64 x, u64 q, u64 mu_hi) {
+    // floor(x * floor(2^128/q) / 2^128) >= floor(x/q) - 1 using only the high word of mu
+    u64 qhat = __umul64hi(x, mu_hi);
+    u64 r = x - qhat * q;
+    r = csub(r, 2 * q);
+    return csub(r, q);
+}
+// signed value -> canonical residue (the reference's `v % q; if (v < 0) v += q`)
+__device__ __forceinline__ u64 signed_mod(long long v, u64 q, u64 mu_hi) {
+    u64 a = v < 0 ? (u64)(-(v + 1)) + 1ull : (u64)v;     // |v| without overflow at INT64_MIN
+    u64 r = reduce64(a, q, mu_hi);
+    return (v < 0 && r) ? q - r : r;
+}
+
+}  // namespace mfhe

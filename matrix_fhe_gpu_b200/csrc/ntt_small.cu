@@ -16,6 +16,7 @@
 //   kGlXnMinusI         X^n - i, natural in -> natural out: A[k] = sum a_j psi^j w^(jk)
 //   kCyclicNatural      X^n - 1, natural in -> natural out (custom_ntt_forward alone)
 #include "ntt_api.h"
+#include "ntt_small.cuh"
 
 namespace mfhe {
 
@@ -26,50 +27,18 @@ template <int LOGN> __device__ __forceinline__ u32 bitrev_n(u32 x) { return __br
 template <int LOGN, bool NATURAL>
 __global__ void __launch_bounds__(kSmallThreads)
 ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
-    constexpr int N = 1 << LOGN, TPP = N / 8, PPB = kSmallThreads / TPP, STRIDE = N + 8;
+    using Net = SmallNet<LOGN>;
+    constexpr int TPP = Net::TPP, PPB = kSmallThreads / TPP, STRIDE = Net::STRIDE;
     __shared__ __align__(16) u64 sm_all[PPB * STRIDE];
     const u32 u = threadIdx.x % TPP, pib = threadIdx.x / TPP;
     const size_t lp = (size_t)blockIdx.x * PPB + pib;
     if (lp >= limb_polys) return;                       // whole polys drop out together (TPP <= 32)
     const u32 limb = lp % limbs;
     const u64 q = T.moduli[limb], q2 = 2 * q;
-    const tw_t* tw = T.tw + ((size_t)limb << LOGN);
     u64* g = data + (lp << LOGN);
     u64* sm = sm_all + pib * STRIDE;
     u64 v[8];
-
-    constexpr int P0 = LOGN - 3;
-    constexpr int P1 = P0 > 3 ? P0 - 3 : 0;
-    constexpr int P2 = P1 > 3 ? P1 - 3 : 0;
-    {
-        const u32 e0 = deposit3(u, P0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = g[e0 + (j << P0)];
-        fwd_pass<LOGN, P0, 7>(v, e0, tw, q, q2);
-        if constexpr (P0 > 0) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) sm[swz(e0 + (j << P0))] = v[j];
-        }
-    }
-    if constexpr (P0 > 0) {
-        __syncwarp();
-        const u32 e1 = deposit3(u, P1);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << P1))];
-        fwd_pass<LOGN, P1, (1 << (P0 - P1)) - 1>(v, e1, tw, q, q2);
-        if constexpr (P1 > 0) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << P1))] = v[j];
-            __syncwarp();
-            const u32 e2 = deposit3(u, P2);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << P2))];
-            fwd_pass<LOGN, P2, (1 << (P1 - P2)) - 1>(v, e2, tw, q, q2);
-        }
-    }
-    static_assert(P2 == 0, "n <= 256");
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { v[j] = csub(v[j], q2); v[j] = csub(v[j], q); }
+    Net::forward(v, g, sm, u, T.tw + ((size_t)limb << LOGN), q, q2);
     // the thread now holds positions 8u .. 8u+7 of the bit-reversed-order result
     if constexpr (NATURAL) {
         __syncwarp();
@@ -89,15 +58,14 @@ ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t li
 template <int LOGN, bool NATURAL>
 __global__ void __launch_bounds__(kSmallThreads)
 ntt_small_inv_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
-    constexpr int N = 1 << LOGN, TPP = N / 8, PPB = kSmallThreads / TPP, STRIDE = N + 8;
+    using Net = SmallNet<LOGN>;
+    constexpr int TPP = Net::TPP, PPB = kSmallThreads / TPP, STRIDE = Net::STRIDE;
     __shared__ __align__(16) u64 sm_all[PPB * STRIDE];
     const u32 u = threadIdx.x % TPP, pib = threadIdx.x / TPP;
     const size_t lp = (size_t)blockIdx.x * PPB + pib;
     if (lp >= limb_polys) return;
     const u32 limb = lp % limbs;
     const u64 q = T.moduli[limb], q2 = 2 * q;
-    const tw_t* itw = T.itw + ((size_t)limb << LOGN);
-    const tw_t ninv = T.ninv[limb], w1n = T.w1n[limb];
     u64* g = data + (lp << LOGN);
     u64* sm = sm_all + pib * STRIDE;
     u64 v[8];
@@ -113,38 +81,10 @@ ntt_small_inv_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t li
             const ulonglong2 t = *reinterpret_cast<const ulonglong2*>(sm + swz(8 * u + 2 * k));
             v[2 * k] = t.x; v[2 * k + 1] = t.y;
         }
-        __syncwarp();
     }
-    constexpr int PL = LOGN - 3;
-    constexpr int P1 = PL < 3 ? PL : 3;
-    constexpr int P2 = PL < 6 ? PL : 6;
-    inv_pass<LOGN, 0, 7>(v, 8 * u, itw, q, q2, ninv, w1n);
-    if constexpr (PL > 0) {
+    const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)limb << LOGN), q, q2, T.ninv[limb], T.w1n[limb]);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) sm[swz(8 * u + j)] = v[j];
-        __syncwarp();
-        const u32 e1 = deposit3(u, P1);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << P1))];
-        inv_pass<LOGN, P1, 7 & ~((1 << (3 - P1)) - 1)>(v, e1, itw, q, q2, ninv, w1n);
-        if constexpr (PL > 3) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << P1))] = v[j];
-            __syncwarp();
-            const u32 e2 = deposit3(u, P2);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << P2))];
-            inv_pass<LOGN, P2, 7 & ~((1 << (P1 + 3 - P2)) - 1)>(v, e2, itw, q, q2, ninv, w1n);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) g[e2 + (j << P2)] = v[j];
-        } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) g[e1 + (j << P1)] = v[j];
-        }
-    } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) g[8 * u + j] = v[j];
-    }
+    for (int j = 0; j < 8; ++j) g[e + (j << Net::PL)] = v[j];
 }
 
 template <int LOGN>

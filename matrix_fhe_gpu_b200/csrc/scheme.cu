@@ -1,0 +1,287 @@
+// scheme.cu -- integer kernels of encrypt / decrypt and the small ciphertext-level ops.
+//
+//   xrow_mul_s   the fused RLWE core: for every row (w, limb, y) of n coefficients
+//                    t = INTT_X( NTT_X(a_row) (.) s[w][limb] ),   out = m - t + e   or   out = m + t
+//                entirely in registers: one read of a, m (and e), one write of out.  Replaces, per
+//                call, src/core/HE.cu:1508-1530 / 1579-1590 = D2D copy + 32 768 launches of Phantom's
+//                64-point NTT (ntt_core.cu:443-450) + pointwise_mul_s_kernel (:509-531) + D2D copy +
+//                32 768 inverse launches + combine_b_kernel / add_poly_kernel (:535-560) + layout passes.
+//   samplers     uniform / gaussian / ternary index-hash streams (HE.cu:564-627, 690-713)
+//   layout       matrix-major <-> poly-major (HE.cu:1330-1368)
+//   ct ops       add_ct_kernel / mul_tensor_kernel (HE.cu:631-669)
+//   trace step   trace.cu:30-161, batched_trace.cu:37-197
+//   gl perm      ntt_core.cu:258-269
+#include "ctx.h"
+#include "ntt_api.h"
+#include "ntt_small.cuh"
+
+namespace mfhe {
+
+__device__ __forceinline__ size_t row_offset(int layout, u32 w, u32 l, u32 y, int n, int L) {
+    return layout == MFHE_LAYOUT_POLY ? (((size_t)w * n + y) * L + l) * n : (((size_t)w * L + l) * n + y) * n;
+}
+
+template <int LOGN>
+__global__ void __launch_bounds__(256)
+xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_tab, size_t rows) {
+    using Net = SmallNet<LOGN>;
+    constexpr int TPP = Net::TPP, PPB = 256 / TPP, STRIDE = Net::STRIDE;
+    __shared__ __align__(16) u64 sm_all[PPB * STRIDE];
+    const u32 u = threadIdx.x % TPP, pib = threadIdx.x / TPP;
+    const size_t rid = (size_t)blockIdx.x * PPB + pib;          // (w * L + l) * n + y
+    if (rid >= rows) return;
+    const u32 y = rid % r.n, wl = rid / r.n, l = wl % r.limbs, w = wl / r.limbs;
+    const u64 q = T.moduli[l], q2 = 2 * q;
+    const ulonglong2 mu = mu_tab[l];
+    u64* sm = sm_all + pib * STRIDE;
+    u64 v[8];
+    Net::forward(v, r.a + row_offset(r.a_layout, w, l, y, r.n, r.limbs), sm, u, T.tw + ((size_t)l << LOGN), q, q2);
+    {
+        const u64* s = r.s + ((size_t)wl << LOGN) + 8 * u;      // key is stored in the same bit-reversed order
+        const ulonglong2 s0 = __ldg((const ulonglong2*)s), s1 = __ldg((const ulonglong2*)s + 1),
+                         s2 = __ldg((const ulonglong2*)s + 2), s3 = __ldg((const ulonglong2*)s + 3);
+        v[0] = mul_barrett(v[0], s0.x, q, mu.x, mu.y); v[1] = mul_barrett(v[1], s0.y, q, mu.x, mu.y);
+        v[2] = mul_barrett(v[2], s1.x, q, mu.x, mu.y); v[3] = mul_barrett(v[3], s1.y, q, mu.x, mu.y);
+        v[4] = mul_barrett(v[4], s2.x, q, mu.x, mu.y); v[5] = mul_barrett(v[5], s2.y, q, mu.x, mu.y);
+        v[6] = mul_barrett(v[6], s3.x, q, mu.x, mu.y); v[7] = mul_barrett(v[7], s3.y, q, mu.x, mu.y);
+    }
+    const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)l << LOGN), q, q2, T.ninv[l], T.w1n[l]);
+#pragma unroll
+    for (int comp = 0; comp < 2; ++comp) {
+        const u64* m = comp ? r.m1 : r.m0;
+        const u64* er = comp ? r.e1 : r.e0;
+        u64* o = comp ? r.o1 : r.o0;
+        if (!o) continue;
+        const size_t mo = row_offset(r.m_layout, w, l, y, r.n, r.limbs), eo = row_offset(r.e_layout, w, l, y, r.n, r.limbs),
+                     oo = row_offset(r.o_layout, w, l, y, r.n, r.limbs);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const u32 pos = e + (j << Net::PL);
+            u64 x = m[mo + pos];
+            if (r.subtract) { x = sub_mod(x, v[j], q); if (er) x = add_mod(x, er[eo + pos], q); }
+            else x = add_mod(x, v[j], q);
+            o[oo + pos] = x;
+        }
+    }
+}
+
+cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulonglong2* mu, cudaStream_t st) {
+    const size_t rows = (size_t)r.phi * r.limbs * r.n;
+#define MFHE_ROW_CASE(LN)                                                                       \
+    case LN: {                                                                                  \
+        constexpr int PPB = 256 / ((1 << LN) / 8);                                              \
+        xrow_mul_s_kernel<LN><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
+        break; }
+    switch (T.logn) {
+        MFHE_ROW_CASE(4) MFHE_ROW_CASE(5) MFHE_ROW_CASE(6) MFHE_ROW_CASE(7) MFHE_ROW_CASE(8)
+        default: return cudaErrorInvalidValue;
+    }
+#undef MFHE_ROW_CASE
+    return cudaGetLastError();
+}
+
+// ---- samplers (stand-alone form; encrypt fuses them into the W-CRT loader, wcrt.cu) -------------------
+__device__ __forceinline__ u64 splitmix64_s(u64 x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+template <int KIND>
+__global__ void sample_kernel(u64* __restrict__ out, const u64* __restrict__ moduli, int n, int limbs, size_t total) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    if (KIND == 2) {                                   // ternary, [w][limb][x]
+        const size_t per = (size_t)limbs * n, off = idx % per, limb = off / n, coeff = off - limb * n, poly = idx / per;
+        const u64 t = (u64)poly * 1315423911ULL + (u64)coeff * 2654435761ULL;
+        const int r = (int)((t * 11400714819323198485ULL) % 3ULL);
+        out[idx] = r == 0 ? 0 : r == 1 ? 1 : moduli[limb] - 1;
+        return;
+    }
+    const size_t n2 = (size_t)n * n, per = (size_t)limbs * n2, off = idx % per, limb = off / n2;
+    const u64 q = moduli[limb];
+    if (KIND == 0) {
+        u64 seed = 123456789ULL + idx;
+        seed = seed * 6364136223846793005ULL + 1442695040888963407ULL;
+        out[idx] = seed % q;
+    } else {
+        const u64 coeff_id = (u64)((idx / per) * n2 + off % n2);
+        const u64 r1 = splitmix64_s(0xD6E8FEB86659FD93ULL ^ coeff_id), r2 = splitmix64_s(r1);
+        const double inv53 = 1.0 / 9007199254740992.0;
+        const double u1 = ((double)(r1 >> 11) + 1.0) * inv53, u2 = ((double)(r2 >> 11) + 1.0) * inv53;
+        const double mag = 3.2 * sqrt(-2.0 * log(u1));
+        const long long z = llround(mag * cos(6.283185307179586 * u2));
+        out[idx] = z >= 0 ? (u64)z : q - (u64)(-z);
+    }
+}
+cudaError_t sample_launch(int kind, u64* out, const u64* moduli, int n, int limbs, int phi, cudaStream_t st) {
+    const size_t total = kind == 2 ? (size_t)phi * limbs * n : (size_t)phi * limbs * n * n;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    if (kind == 0) sample_kernel<0><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
+    else if (kind == 1) sample_kernel<1><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
+    else sample_kernel<2><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
+    return cudaGetLastError();
+}
+
+// ---- layout -------------------------------------------------------------------------------------------
+__global__ void layout_kernel(const u64* __restrict__ in, u64* __restrict__ out, int n, int limbs, size_t total2,
+                              int in_layout, int out_layout) {
+    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;     // pairs of words
+    if (i2 >= total2) return;
+    const size_t idx = i2 * 2;
+    const u32 x = idx % n; const size_t t = idx / n;
+    const u32 y = t % n, wl = t / n, l = wl % limbs, w = wl / limbs;
+    const ulonglong2 v = *(const ulonglong2*)(in + row_offset(in_layout, w, l, y, n, limbs) + x);
+    *(ulonglong2*)(out + row_offset(out_layout, w, l, y, n, limbs) + x) = v;
+}
+cudaError_t layout_launch(const u64* in, u64* out, int n, int limbs, int phi, int in_layout, int out_layout, cudaStream_t st) {
+    const size_t total2 = (size_t)phi * limbs * n * n / 2;
+    layout_kernel<<<(unsigned)((total2 + 255) / 256), 256, 0, st>>>(in, out, n, limbs, total2, in_layout, out_layout);
+    return cudaGetLastError();
+}
+
+// ---- ciphertext add / tensor product -----------------------------------------------------------------
+__device__ __forceinline__ int ct_limb(size_t idx, int n, int limbs, int ref_index) {
+    // reference kernels: limb = (idx % (limbs*n)) / n, i.e. the POLY formula whatever the data layout
+    return ref_index ? (int)((idx / n) % limbs) : (int)((idx / ((size_t)n * n)) % limbs);
+}
+__global__ void ct_add_kernel(const u64* __restrict__ c1, const u64* __restrict__ c2, u64* __restrict__ res,
+                              const u64* __restrict__ moduli, size_t T, int n, int limbs, int ref_index) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= T) return;
+    const u64 q = moduli[ct_limb(idx, n, limbs, ref_index)];
+    // the reference's add_mod (common.cuh:12-14 -> Phantom add_uint64_uint64_mod) is (a+b) - q*(a+b >= q)
+    res[idx] = csub(c1[idx] + c2[idx], q);
+    res[T + idx] = csub(c1[T + idx] + c2[T + idx], q);
+}
+cudaError_t ct_add_launch(const u64* c1, const u64* c2, u64* res, const u64* moduli, size_t T, int n, int limbs,
+                          int ref_index, cudaStream_t st) {
+    ct_add_kernel<<<(unsigned)((T + 255) / 256), 256, 0, st>>>(c1, c2, res, moduli, T, n, limbs, ref_index);
+    return cudaGetLastError();
+}
+__global__ void ct_mul_kernel(const u64* __restrict__ c1, const u64* __restrict__ c2, u64* __restrict__ d0,
+                              u64* __restrict__ d1, u64* __restrict__ d2, const u64* __restrict__ moduli,
+                              const ulonglong2* __restrict__ mu_tab, size_t T, int n, int limbs, int ref_index) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= T) return;
+    const int l = ct_limb(idx, n, limbs, ref_index);
+    const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
+    const u64 b1 = c1[idx], a1 = c1[T + idx], b2 = c2[idx], a2 = c2[T + idx];
+    d0[idx] = mul_barrett(b1, b2, q, mu.x, mu.y);
+    d1[idx] = add_mod(mul_barrett(b1, a2, q, mu.x, mu.y), mul_barrett(a1, b2, q, mu.x, mu.y), q);
+    d2[idx] = mul_barrett(a1, a2, q, mu.x, mu.y);
+}
+cudaError_t ct_mul_launch(const u64* c1, const u64* c2, u64* d0, u64* d1, u64* d2, const u64* moduli, const ulonglong2* mu,
+                          size_t T, int n, int limbs, int ref_index, cudaStream_t st) {
+    ct_mul_kernel<<<(unsigned)((T + 255) / 256), 256, 0, st>>>(c1, c2, d0, d1, d2, moduli, mu, T, n, limbs, ref_index);
+    return cudaGetLastError();
+}
+
+// ---- trace step -----------------------------------------------------------------------------------------
+// trace.cu:30-62 / batched_trace.cu:37-79:  B'[(-j mod n)][k] = (a, -b) for j = 0, (-b, -a) otherwise
+__global__ void trace_map_kernel(const u64* __restrict__ Br, const u64* __restrict__ Bi, u64* __restrict__ Bpr,
+                                 u64* __restrict__ Bpi, const u64* __restrict__ moduli, int n, int limbs, size_t total) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t n2 = (size_t)n * n, mat = idx / n2, pos = idx % n2;
+    const int j = (int)(pos / n), k = (int)(pos % n), l = (int)(mat % limbs);
+    const u64 q = moduli[l];
+    const size_t dst = mat * n2 + (size_t)((n - j) & (n - 1)) * n + k;
+    const u64 a = Br[idx], b = Bi[idx];
+    if (j == 0) { Bpr[dst] = a; Bpi[dst] = neg_mod(b, q); }
+    else { Bpr[dst] = neg_mod(b, q); Bpi[dst] = neg_mod(a, q); }
+}
+cudaError_t trace_map_launch(const u64* Br, const u64* Bi, u64* Bpr, u64* Bpi, const u64* moduli, int n, int limbs,
+                             int batch, cudaStream_t st) {
+    const size_t total = (size_t)batch * limbs * n * n;
+    trace_map_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(Br, Bi, Bpr, Bpi, moduli, n, limbs, total);
+    return cudaGetLastError();
+}
+
+// trace.cu:77-120 / batched_trace.cu:99-146:  C = n * A * B'^T (complex, mod q) for one (batch, limb) per CTA.
+// Operands are staged transposed in shared memory ([t][row], padded), the four real sums
+// sum ar*br, sum ai*bi, sum ar*bi, sum ai*br accumulate lazily in 128 bits (n * q^2 < 2^128) and are
+// reduced once -- the same residues as the reference's per-term `u128 %` chain.
+struct acc128 { u64 lo, hi; };
+__device__ __forceinline__ void mac128(acc128& s, u64 a, u64 b) {
+    const u64 lo = a * b, hi = __umul64hi(a, b);
+    s.lo += lo; s.hi += hi + (s.lo < lo);
+}
+__global__ void __launch_bounds__(256)
+trace_gemm_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, const u64* __restrict__ Bpr,
+                  const u64* __restrict__ Bpi, u64* __restrict__ Cr, u64* __restrict__ Ci,
+                  const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu_tab, int n, int limbs) {
+    extern __shared__ u64 sm_tr[];
+    const int ld = n + 1;
+    u64 *sAr = sm_tr, *sAi = sAr + (size_t)n * ld, *sBr = sAi + (size_t)n * ld, *sBi = sBr + (size_t)n * ld;
+    const size_t n2 = (size_t)n * n, base = (size_t)blockIdx.x * n2;
+    const int l = blockIdx.x % limbs;
+    const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
+    for (size_t i = threadIdx.x; i < n2; i += blockDim.x) {
+        const int row = (int)(i / n), t = (int)(i % n);
+        sAr[t * ld + row] = Ar[base + i]; sAi[t * ld + row] = Ai[base + i];
+        sBr[t * ld + row] = Bpr[base + i]; sBi[t * ld + row] = Bpi[base + i];
+    }
+    __syncthreads();
+    const u64 nm = reduce64((u64)n, q, mu.y);
+    for (size_t o = threadIdx.x; o < n2; o += blockDim.x) {
+        const int row = (int)(o / n), col = (int)(o % n);
+        acc128 rr = {0, 0}, ii = {0, 0}, ri = {0, 0}, ir = {0, 0};
+        for (int t = 0; t < n; ++t) {
+            const u64 ar = sAr[t * ld + row], ai = sAi[t * ld + row], br = sBr[t * ld + col], bi = sBi[t * ld + col];
+            mac128(rr, ar, br); mac128(ii, ai, bi); mac128(ri, ar, bi); mac128(ir, ai, br);
+        }
+        const u64 vr = sub_mod(reduce128(rr.lo, rr.hi, q, mu.x, mu.y), reduce128(ii.lo, ii.hi, q, mu.x, mu.y), q);
+        const u64 vi = add_mod(reduce128(ri.lo, ri.hi, q, mu.x, mu.y), reduce128(ir.lo, ir.hi, q, mu.x, mu.y), q);
+        Cr[base + o] = mul_barrett(vr, nm, q, mu.x, mu.y);
+        Ci[base + o] = mul_barrett(vi, nm, q, mu.x, mu.y);
+    }
+}
+cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
+                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st) {
+    const size_t smem = 4 * (size_t)n * (n + 1) * sizeof(u64);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(trace_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    trace_gemm_kernel<<<(unsigned)(batch * limbs), 256, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, n, limbs);
+    return cudaGetLastError();
+}
+
+// trace.cu:132-161 / batched_trace.cu:163-197: limbs >= 3 are multiplied by 0, as in the reference
+__global__ void trace_rescale_kernel(u64* __restrict__ Cr, u64* __restrict__ Ci, const u64* __restrict__ moduli,
+                                     const ulonglong2* __restrict__ mu_tab, int n, int limbs, size_t total, u64 inv0,
+                                     u64 inv1, u64 inv2) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int l = (int)((idx / ((size_t)n * n)) % limbs);
+    const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
+    const u64 inv = l == 0 ? inv0 : l == 1 ? inv1 : l == 2 ? inv2 : 0;
+    Cr[idx] = mul_barrett(Cr[idx], inv, q, mu.x, mu.y);
+    Ci[idx] = mul_barrett(Ci[idx], inv, q, mu.x, mu.y);
+}
+cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
+                                 u64 inv0, u64 inv1, u64 inv2, cudaStream_t st) {
+    const size_t total = (size_t)batch * limbs * n * n;
+    trace_rescale_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(Cr, Ci, moduli, mu, n, limbs, total, inv0, inv1, inv2);
+    return cudaGetLastError();
+}
+
+// ---- GL permutation: ntt_core.cu:258-269  out[perm[x]] = in[x] along x ---------------------------------
+__global__ void gl_perm_kernel(const u64* __restrict__ in, u64* __restrict__ out, const uint32_t* __restrict__ perm,
+                               int n, size_t total) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const size_t base = idx - idx % n;
+    out[base + perm[idx % n]] = in[idx];
+}
+cudaError_t gl_perm_launch(const u64* in, u64* out, const uint32_t* perm, int limbs, int batch, int n, cudaStream_t st) {
+    const size_t total = (size_t)batch * limbs * n;
+    gl_perm_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, out, perm, n, total);
+    return cudaGetLastError();
+}
+
+}  // namespace mfhe

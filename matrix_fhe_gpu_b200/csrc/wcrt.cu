@@ -1,0 +1,213 @@
+// wcrt.cu -- the W-CRT (evaluation at / interpolation from the primitive p-th roots of unity mod q_l)
+// as one tiled modular GEMM per limb:   out[o][col] = sum_i tab[limb][i][o] * in[i][col]  (mod q_limb).
+//
+// Replaces src/core/HE.cu:716-781 (wntt_forward_matrix_kernel / wntt_inverse_matrix_kernel: one thread
+// per output, phi `unsigned __int128 %` modmuls each, table and input re-read from global memory per
+// thread), :1245-1270 (vector form), and the per-limb inner loops of :1029-1114 (centred forms).
+// Exact integer arithmetic, so the canonical residues are those of the reference's
+// add_mod(acc, mul_mod(a, w)) chain.
+//
+//   * 64 x 64 output tile per CTA, K tiles of 16 double-buffered through shared memory, 4 x 4 outputs
+//     per thread in registers;
+//   * no modular reduction inside the K loop.  For q < 2^52 (the reference's 35/45-bit primes) both
+//     operands are split into 26-bit halves and the three partial sums
+//         S0 = sum a0 w0,  S1 = sum (a0 w1 + a1 w0),  S2 = sum a1 w1
+//     are kept in plain 64-bit registers (phi * 2^53 < 2^64): 4 IMAD.WIDE.U32 per MAC and no carry
+//     handling; one 128-bit Barrett reduction per output at the end.  Larger q (< 2^59) accumulates
+//     the 128-bit products directly;
+//   * the loader is a template parameter, so samplers (uniform a, gaussian e), the int64 centred
+//     input and the quantiser (llround(z * delta) mod q) feed the GEMM without a round trip through
+//     HBM, and the epilogue writes either layout (and an optional second copy) directly.
+#include "ctx.h"
+
+namespace mfhe {
+
+constexpr int TO = 64, TC = 64, TK = 16, WTHREADS = 256;
+constexpr u32 MASK26 = (1u << 26) - 1u;
+
+__device__ __forceinline__ size_t poly_set_addr(int layout, int w, int l, int c, int n, int cols, int L) {
+    if (layout == MFHE_LAYOUT_POLY) {
+        const int y = c / n, x = c - y * n;
+        return (((size_t)w * n + y) * L + l) * n + x;
+    }
+    return ((size_t)w * L + l) * cols + c;
+}
+
+__device__ __forceinline__ u64 splitmix64_dev(u64 x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+// src/core/HE.cu:590-627: one centred integer per logical coefficient [w][pos], same in every limb
+__device__ __forceinline__ long long gaussian_noise_value(u64 coeff_id) {
+    const u64 r1 = splitmix64_dev(0xD6E8FEB86659FD93ULL ^ coeff_id), r2 = splitmix64_dev(r1);
+    const double inv53 = 1.0 / 9007199254740992.0;
+    const double u1 = ((double)(r1 >> 11) + 1.0) * inv53, u2 = ((double)(r2 >> 11) + 1.0) * inv53;
+    const double mag = 3.2 * sqrt(-2.0 * log(u1));
+    return llround(mag * cos(6.283185307179586 * u2));
+}
+// src/core/HE.cu:564-578
+__device__ __forceinline__ u64 uniform_value(u64 idx, u64 q, u64 mu_hi) {
+    u64 seed = 123456789ULL + idx;
+    seed = seed * 6364136223846793005ULL + 1442695040888963407ULL;
+    return reduce64(seed, q, mu_hi);
+}
+
+// four consecutive columns of input row i, as canonical residues
+template <int SRC>
+__device__ __forceinline__ void load_in4(const WcrtArgs& a, int i, int l, int c, u64 q, u64 mu_hi, u64 (&v)[4]) {
+    if (i >= a.phi || c >= a.cols) { v[0] = v[1] = v[2] = v[3] = 0; return; }
+    if constexpr (SRC == kSrcMem) {
+        const u64* p = (const u64*)a.in + poly_set_addr(a.in_layout, i, l, c, a.n, a.cols, a.limbs);
+        const ulonglong2 x = __ldg((const ulonglong2*)p), y = __ldg((const ulonglong2*)p + 1);
+        v[0] = x.x; v[1] = x.y; v[2] = y.x; v[3] = y.y;
+    } else if constexpr (SRC == kSrcI64) {
+        const long long* p = (const long long*)a.in + (size_t)i * a.cols + c;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = signed_mod(p[j], q, mu_hi);
+    } else if constexpr (SRC == kSrcQuantRe || SRC == kSrcQuantIm) {
+        const double2* p = (const double2*)a.in + (size_t)i * a.cols + c;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const double2 z = p[j];
+            v[j] = signed_mod(llround((SRC == kSrcQuantRe ? z.x : z.y) * a.delta), q, mu_hi);
+        }
+    } else if constexpr (SRC == kSrcUniform) {
+        const u64 base = ((u64)i * a.limbs + l) * a.cols + c;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = uniform_value(base + j, q, mu_hi);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const long long z = gaussian_noise_value((u64)i * a.cols + c + j);
+            v[j] = z >= 0 ? (u64)z : q - (u64)(-z);
+        }
+    }
+}
+
+template <int SRC, bool SPLIT>
+__global__ void __launch_bounds__(WTHREADS)
+wcrt_gemm_kernel(const WcrtArgs a) {
+    __shared__ __align__(16) u64 sTab[2][TK][TO];
+    __shared__ __align__(16) u64 sIn[2][TK][TC];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int lrel = blockIdx.z, l = a.limb0 + lrel;
+    const int o0 = blockIdx.y * TO, c0 = blockIdx.x * TC;
+    const u64 q = a.moduli[l];
+    const ulonglong2 mu = a.mu[l];
+    const u64* tab = a.tab + (size_t)l * a.phi * a.phi;
+    // staging: row lk of the K tile, 4 consecutive entries at column group lg
+    const int lk = t >> 4, lg = (t & 15) << 2;
+
+    u64 rt[4], ri[4];
+    auto fetch = [&](int k0) {
+        const int i = k0 + lk;
+        if (i < a.phi && o0 + lg < a.phi) {
+            const ulonglong2 x = __ldg((const ulonglong2*)(tab + (size_t)i * a.phi + o0 + lg));
+            const ulonglong2 y = __ldg((const ulonglong2*)(tab + (size_t)i * a.phi + o0 + lg) + 1);
+            rt[0] = x.x; rt[1] = x.y; rt[2] = y.x; rt[3] = y.y;
+        } else { rt[0] = rt[1] = rt[2] = rt[3] = 0; }
+        load_in4<SRC>(a, i, SRC == kSrcMem ? lrel : l, c0 + lg, q, mu.y, ri);
+    };
+    auto stash = [&](int buf) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            sTab[buf][lk][lg + j] = rt[j];
+            sIn[buf][lk][lg + j] = SPLIT ? ((ri[j] & MASK26) | ((ri[j] >> 26) << 32)) : ri[j];
+        }
+    };
+
+    u64 s0[4][4], s1[4][4], s2[4][4];       // SPLIT: three partial sums; else {lo, hi, unused}
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) s0[i][j] = s1[i][j] = s2[i][j] = 0;
+
+    fetch(0);
+    stash(0);
+    __syncthreads();
+    const int ktiles = (a.phi + TK - 1) / TK;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * TK);
+#pragma unroll
+        for (int k = 0; k < TK; ++k) {
+            u64 av[4], bv[4];
+            {
+                const ulonglong2 x = *(const ulonglong2*)&sTab[buf][k][ty * 4], y = *(const ulonglong2*)&sTab[buf][k][ty * 4 + 2];
+                av[0] = x.x; av[1] = x.y; av[2] = y.x; av[3] = y.y;
+                const ulonglong2 z = *(const ulonglong2*)&sIn[buf][k][tx * 4], w = *(const ulonglong2*)&sIn[buf][k][tx * 4 + 2];
+                bv[0] = z.x; bv[1] = z.y; bv[2] = w.x; bv[3] = w.y;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if constexpr (SPLIT) {
+                        const u32 a0 = (u32)av[i], a1 = (u32)(av[i] >> 32), b0 = (u32)bv[j], b1 = (u32)(bv[j] >> 32);
+                        s0[i][j] += (u64)a0 * b0;
+                        s1[i][j] += (u64)a0 * b1;
+                        s1[i][j] += (u64)a1 * b0;
+                        s2[i][j] += (u64)a1 * b1;
+                    } else {
+                        const u64 lo = av[i] * bv[j], hi = __umul64hi(av[i], bv[j]);
+                        s0[i][j] += lo;
+                        s1[i][j] += hi + (s0[i][j] < lo);
+                    }
+                }
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+
+    // epilogue: one Barrett reduction per output, 4 consecutive columns per store
+    const int c = c0 + tx * 4;
+    if (c >= a.cols) return;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int o = o0 + ty * 4 + i;
+        if (o >= a.phi) continue;
+        u64 r[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            u64 lo, hi;
+            if constexpr (SPLIT) {
+                lo = s0[i][j]; hi = 0;
+                u64 x = s1[i][j] << 26; lo += x; hi += (s1[i][j] >> 38) + (lo < x);
+                x = s2[i][j] << 52; lo += x; hi += (s2[i][j] >> 12) + (lo < x);
+            } else { lo = s0[i][j]; hi = s1[i][j]; }
+            r[j] = reduce128(lo, hi, q, mu.x, mu.y);
+        }
+        const size_t off = poly_set_addr(a.out_layout, o, lrel, c, a.n, a.cols, a.limbs);
+        *(ulonglong2*)(a.out + off) = make_ulonglong2(r[0], r[1]);
+        *((ulonglong2*)(a.out + off) + 1) = make_ulonglong2(r[2], r[3]);
+        if (a.out2) {
+            *(ulonglong2*)(a.out2 + off) = make_ulonglong2(r[0], r[1]);
+            *((ulonglong2*)(a.out2 + off) + 1) = make_ulonglong2(r[2], r[3]);
+        }
+    }
+}
+
+template <int SRC>
+static cudaError_t launch_src(const WcrtArgs& a, dim3 grid, cudaStream_t st) {
+    if (a.split) wcrt_gemm_kernel<SRC, true><<<grid, WTHREADS, 0, st>>>(a);
+    else         wcrt_gemm_kernel<SRC, false><<<grid, WTHREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st) {
+    if (a.cols % 4 || a.phi % 4 || a.n % 4) return cudaErrorInvalidValue;
+    dim3 grid((a.cols + TC - 1) / TC, (a.phi + TO - 1) / TO, a.limbs);
+    switch (a.source) {
+        case kSrcMem:     return launch_src<kSrcMem>(a, grid, st);
+        case kSrcI64:     return launch_src<kSrcI64>(a, grid, st);
+        case kSrcQuantRe: return launch_src<kSrcQuantRe>(a, grid, st);
+        case kSrcQuantIm: return launch_src<kSrcQuantIm>(a, grid, st);
+        case kSrcUniform: return launch_src<kSrcUniform>(a, grid, st);
+        case kSrcGauss:   return launch_src<kSrcGauss>(a, grid, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace mfhe
