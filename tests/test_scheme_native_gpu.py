@@ -1,0 +1,107 @@
+"""The matrix pipeline at the reference's native shape (n = 64, p = 771, phi = 512, L = 11, delta = 2^35):
+one (re, im) pair = 2 x 176 MiB of message evals, 4 x 176 MiB of ciphertext.
+
+  * the three CMake-built end-to-end drivers of the reference, restated: main.cu (< 1e-4),
+    test_encode_encrypt_decrypt_decode_wcrt.cu (< 1e-3), test_encode_decode_wcrt.cu (zero key, < 1e-3);
+  * ciphertext words of one full encrypt_pair_with, bit-exact against the CPU oracle (about half a minute of
+    host time: three dense W-CRTs of 11.8 G modmuls each);
+  * W-CRT columns sampled against Python-integer evaluation; round trips on the full buffers.
+"""
+import numpy as np
+import pytest
+
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def dev(x, device):
+    import torch
+    x = np.ascontiguousarray(x)
+    return torch.from_numpy(x.view(np.int64) if x.dtype == np.uint64 else x).to(device)
+
+
+def host(t):
+    a = t.cpu().numpy()
+    return a.view(np.uint64) if a.dtype == np.int64 else a
+
+
+@pytest.fixture(scope="module")
+def G(cuda_device):
+    import matrix_fhe_gpu_b200.scheme as S
+    return S, S.Context()
+
+
+@pytest.fixture(scope="module")
+def Or():
+    return O.SchemeCtx()
+
+
+def msg(kind, phi=512, n2=4096):
+    ell, i = np.meshgrid(np.arange(phi, dtype=np.float64), np.arange(n2, dtype=np.float64), indexing="ij")
+    if kind == "big":
+        v = ell * 10000.0 + i; return (v - 1j * v).reshape(-1)
+    if kind == "e2e":
+        v = ell + 0.001 * i; return (v - 1j * v).reshape(-1)
+    return ((ell + 1e-5 * i) + 1j * (ell - 1e-5 * i)).reshape(-1)
+
+
+def test_native_tables(G, Or):
+    S, g = G
+    assert (g.n, g.phi, g.L, g.big_words) == (64, 512, 11, 7)
+    assert [g.eta(l) for l in range(3)] == [10467697596351, 6077882864, 12895515671]
+    for l in (0, 1, 10):
+        assert (g.wcrt_table(l) == Or.wntt()[l]).all() and (g.wcrt_table(l, True) == Or.wntt(True)[l]).all()
+    t, r = g.crt_tables(), Or.crt()
+    assert all((t[k] == r[k]).all() for k in t)
+
+
+def test_native_reference_drivers(G, cuda_device):
+    import torch
+    S, g = G
+    sk = g.generate_secret_key()
+    for kind, thr in (("main", 1e-4), ("e2e", 1e-3)):
+        m = msg(kind)
+        re, im = g.encode_to_wntt_eval(dev(m, cuda_device))
+        cr, ci = g.encrypt_pair(re, im, sk)
+        out = host(g.decrypt_and_decode(cr, ci, sk))
+        err = np.abs(out - m).max()
+        print(f"native {kind}: max_err = {err:.3e}")
+        assert err < thr
+    m = msg("big")
+    re, im = g.encode_to_wntt_eval(dev(m, cuda_device))
+    cr, ci = g.allocate_ciphertext(), g.allocate_ciphertext()
+    cr[: g.T] = re; ci[: g.T] = im
+    err = np.abs(host(g.decrypt_and_decode(cr, ci, torch.zeros_like(sk))) - m).max()
+    print(f"native zero-key big: max_err = {err:.3e}")
+    assert err < 1e-3 and err <= 2.0 ** -20 * np.abs(m).max()
+
+
+def test_native_wcrt_sampled_columns_and_roundtrip(G, Or, cuda_device):
+    S, g = G
+    a = g.sample_uniform()
+    ev = g.wntt_forward_matrix(a, S.MATRIX, S.MATRIX)
+    assert (host(g.wntt_inverse_matrix(ev, S.MATRIX, S.MATRIX)) == host(a)).all()
+    x = host(a).reshape(512, 11, 4096); y = host(ev).reshape(512, 11, 4096)
+    assert (host(a) == Or.sample_uniform()).all()
+    V = Or.wntt()
+    rng = np.random.default_rng(0)
+    for _ in range(12):
+        l, c, w = int(rng.integers(11)), int(rng.integers(4096)), int(rng.integers(512))
+        q = int(Or.moduli[l])
+        assert int(y[w, l, c]) == sum(int(V[l, w, r]) * int(x[r, l, c]) for r in range(512)) % q
+
+
+def test_native_encrypt_bit_exact_vs_oracle(G, Or, cuda_device):
+    S, g = G
+    sk = g.generate_secret_key()
+    assert (host(sk) == Or.keygen()).all()
+    rng = np.random.default_rng(1)
+    q = Or.moduli.reshape(1, -1, 1)
+    m_re = (rng.integers(0, 2 ** 63, size=(512, 11, 4096), dtype=np.uint64) % q).reshape(-1)
+    m_im = (rng.integers(0, 2 ** 63, size=(512, 11, 4096), dtype=np.uint64) % q).reshape(-1)
+    a = host(g.sample_uniform()); e = host(g.sample_gaussian())
+    cr, ci = g.encrypt_pair(dev(m_re, cuda_device), dev(m_im, cuda_device), sk)
+    ocr, oci = Or.encrypt_pair_with(m_re, m_im, host(sk), a, e, e)
+    assert (host(cr) == ocr).all() and (host(ci) == oci).all()
+    assert (host(g.decrypt_to_eval(cr, sk, S.POLY)) == Or.decrypt_to_eval(ocr, host(sk))).all()
