@@ -109,7 +109,7 @@ typedef struct mfhe_ctx mfhe_ctx;
 #define MFHE_LAYOUT_POLY   1
 
 typedef struct mfhe_params {
-    int n;                   /* MATRIX_N, power of two in 8..256                                  */
+    int n;                   /* MATRIX_N: 16, 32 or 64                                             */
     int f;                   /* odd prime; p = 3 f, phi = 2 (f - 1).  Reference: 257               */
     int num_limbs;           /* RNS_NUM_LIMBS                                                      */
     const uint64_t *moduli;  /* each = 1 mod lcm(2n, p), < 2^59                                    */
@@ -135,6 +135,9 @@ int mfhe_ctx_get_wcrt_table(const mfhe_ctx *ctx, int limb, int inverse, uint64_t
 int mfhe_ctx_get_crt(const mfhe_ctx *ctx, int which, uint64_t *h_out);
 /* the n-point X-axis plan (Phantom negacyclic) owned by the context: get_xy_ntt_table, HE.cu:429-435 */
 const mfhe_ntt_plan *mfhe_ctx_xy_plan(const mfhe_ctx *ctx);
+/* device copy of the XY Vandermonde matrices the reference keeps as public Encoder members
+ * (encoder.cuh:46-49; encoder.cu:425-444): which = 0 V, 1 V^T, 2 V^-1, 3 (V^-1)^T; d_out n*n complex */
+int mfhe_ctx_copy_xy_matrix(const mfhe_ctx *ctx, int which, double *d_out, void *stream);
 
 /* ---- W-CRT: wntt_forward_matrix / wntt_inverse_matrix (HE.cu:437-452, 716-781) with explicit
  * layouts (reference: forward MATRIX -> POLY, inverse POLY -> MATRIX); out must not alias in. */

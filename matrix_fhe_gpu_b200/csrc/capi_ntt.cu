@@ -115,8 +115,10 @@ static int run(const mfhe_ntt_plan* p, bool fwd, uint64_t* d, size_t batch, int 
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t e;
     if (p->logn <= 8) {
-        if (ls != 0 || lc != p->L) return fail(MFHE_EUNSUPPORTED, "ntt: limb windows need logn >= 12");
-        e = ntt_small_launch(fwd, (u64*)d, p->small(), p->L, batch, st);
+        SmallTables t = p->small();                 // limb window = the same tables seen from limb `ls`
+        t.moduli += ls; t.ninv += ls; t.w1n += ls;
+        t.tw += (size_t)ls << p->logn; t.itw += (size_t)ls << p->logn;
+        e = ntt_small_launch(fwd, (u64*)d, t, lc, batch, st);
     } else {
         e = ntt_flat_launch(fwd, (u64*)d, p->flat(), ls, lc, batch, p->chunk, st);
     }

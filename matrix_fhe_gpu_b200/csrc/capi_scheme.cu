@@ -172,6 +172,11 @@ extern "C" int mfhe_ctx_get_crt(const mfhe_ctx* c, int which, uint64_t* h) {
     return MFHE_OK;
 }
 extern "C" const mfhe_ntt_plan* mfhe_ctx_xy_plan(const mfhe_ctx* c) { return c ? c->xy_plan : nullptr; }
+extern "C" int mfhe_ctx_copy_xy_matrix(const mfhe_ctx* c, int which, double* d_out, void* s) {
+    if (!c || !d_out || which < 0 || which > 3) return fail(MFHE_EINVAL, "copy_xy_matrix: bad argument");
+    const double2* src = which == 0 ? c->d_xyV : which == 1 ? c->d_xyVT : which == 2 ? c->d_xyVinv : c->d_xyVinvT;
+    return done(cudaMemcpyAsync(d_out, src, c->n2() * sizeof(double2), cudaMemcpyDeviceToDevice, S(s)), "copy_xy_matrix");
+}
 
 // ---- W-CRT ------------------------------------------------------------------------------------------
 static int wcrt_run(mfhe_ctx* c, bool inverse, const uint64_t* in, uint64_t* out, int il, int ol, void* s, const char* who) {
