@@ -44,6 +44,66 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+L24_EXTRA = [17194410241, 17194804993, 17195989249, 17196581377, 17196976129, 17197963009, 17199936769, 17201318401,
+             17201515777, 17203884289, 17206844929, 17207437057, 17209608193]
+
+
+def secondary_metrics(dev, world, dist, pairs_per_rank=2):
+    """BASELINE configs 3 and 4 on the matrix pipeline (native ring n=64, p=771): device-timed, reported
+    next to the headline.  Every rank runs its own (re, im) pairs: batch-sharded, no collective."""
+    import torch
+    import matrix_fhe_gpu_b200.scheme as S
+    out = {}
+
+    def timed(fn, reps):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        fn(); torch.cuda.synchronize()
+        ev[0].record()
+        for _ in range(reps):
+            fn()
+        ev[1].record(); torch.cuda.synchronize()
+        t = torch.tensor([ev[0].elapsed_time(ev[1]) / reps], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for L, tag in ((11, "config3_encode_decode_L11"), (24, "config4_pipeline_L24")):
+        mods = (S.REF_MODULI + L24_EXTRA)[:L]
+        g = S.Context(moduli=mods)
+        ell, i = np.meshgrid(np.arange(g.phi, dtype=np.float64), np.arange(g.n2, dtype=np.float64), indexing="ij")
+        m = torch.from_numpy((ell + 0.001 * i) * (1 - 1j)).reshape(-1).to(dev)
+        sk = g.generate_secret_key()
+        re, im = g.encode_to_wntt_eval(m)
+        cr, ci = g.encrypt_pair(re, im, sk)
+        dec = g.decrypt_and_decode(cr, ci, sk)
+        err = float((dec - m).abs().max())
+        assert err < 1e-3, err
+        if L == 11:
+            zero = torch.zeros_like(sk)
+            ct_r, ct_i = g.allocate_ciphertext(), g.allocate_ciphertext()
+
+            def loop():                          # test_encode_decode_wcrt.cu: encode -> (b = m, a = 0, s = 0) -> decode
+                r, q = g.encode_to_wntt_eval(m)
+                ct_r[: g.T] = r; ct_i[: g.T] = q
+                g.decrypt_and_decode(ct_r, ct_i, zero, dec)
+            out[tag] = {"ms_per_batch": timed(loop, 3), "encode_ms": timed(lambda: g.encode_to_wntt_eval(m), 3),
+                        "decrypt_decode_ms": timed(lambda: g.decrypt_and_decode(ct_r, ct_i, zero, dec), 3),
+                        "batch": "512 lanes x 64x64 complex fp64 (2^21 values)", "max_err": err}
+        else:
+            def pipe():
+                for _ in range(pairs_per_rank):
+                    r, q = g.encode_to_wntt_eval(m)
+                    g.encrypt_pair(r, q, sk, cr, ci)
+                    g.decrypt_and_decode(cr, ci, sk, dec)
+            ms = timed(pipe, 2)
+            out[tag] = {"pairs_per_s": world * pairs_per_rank / (ms * 1e-3), "ciphertexts_per_s": 2 * world * pairs_per_rank / (ms * 1e-3),
+                        "ms_per_pair": ms / pairs_per_rank, "pairs_per_rank_per_step": pairs_per_rank, "max_err": err,
+                        "note": "encode -> encrypt_pair -> decrypt_and_decode, one (re, im) pair = 2 ciphertexts of 768 MiB"}
+        del g
+        torch.cuda.empty_cache()
+    return out
+
+
 class ClockSampler:
     """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -144,6 +204,7 @@ def main():
                     help="limb-polys per kernel pair (L2-resident chunking); -1 = library default")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the matrix-pipeline secondary metrics")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -233,6 +294,11 @@ def main():
     assert (hnp.reshape(x.shape)[0] == x[0]).all()
     nbytes = x.nbytes
 
+    secondary = None
+    if not args.no_secondary:
+        del d
+        torch.cuda.empty_cache()
+        secondary = secondary_metrics(dev, world, dist if world > 1 else None)
     if rank == 0:
         peak, peak_src = peaks()
         t_fwd = statistics.median(tf) * 1e-3
@@ -263,6 +329,8 @@ def main():
                          "ms_forward": t_fwd * 1e3, "ms_inverse": t_inv * 1e3,
                          "pair_frac": (2 * algo / (t_fwd + t_inv) / 1e9) / peak},
         }
+        if secondary is not None:
+            line["secondary"] = secondary
         if not args.no_cpu:
             n_lp, times, cores = cpu_sample(2 * LIMBS, 3)
             line["cpu_baseline"] = {"value": n_lp / min(times), "unit": "limb-polys/s", "cores": cores,

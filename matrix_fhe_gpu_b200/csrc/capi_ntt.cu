@@ -1,4 +1,5 @@
 // capi_ntt.cu -- C ABI (include/mfhe.h) for the NTT family: plans, transforms, pointwise ops.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -138,22 +139,46 @@ extern "C" int mfhe_ntt_inverse_limbs(const mfhe_ntt_plan* p, uint64_t* d, size_
     return run(p, false, d, batch, ls, lc, s);
 }
 
+// Host-buffer path: the batch is cut into chunks of whole polys and pipelined over three streams so
+// that the H2D copy of chunk i+1, the transform of chunk i and the D2H copy of chunk i-1 overlap
+// (PCIe is full duplex; with pinned host memory the step costs ~max(H2D, D2H) instead of their sum).
 static int run_host(mfhe_ntt_plan* p, bool fwd, uint64_t* h, size_t batch) {
     if (!p || (!h && batch)) return fail(MFHE_EINVAL, "ntt_host: NULL plan or data");
     if (batch == 0) return MFHE_OK;
-    const size_t bytes = (batch * p->L << p->logn) * sizeof(uint64_t);
+    const size_t poly_words = (size_t)p->L << p->logn;
+    const size_t bytes = batch * poly_words * sizeof(uint64_t);
     cudaError_t e;
     if (bytes > p->stage_bytes) {
         cudaFree(p->d_stage); p->d_stage = nullptr; p->stage_bytes = 0;
         if ((e = cudaMalloc((void**)&p->d_stage, bytes)) != cudaSuccess) return cuda_fail(e, "ntt_host staging");
         p->stage_bytes = bytes;
     }
-    if ((e = cudaMemcpyAsync(p->d_stage, h, bytes, cudaMemcpyHostToDevice, 0)) != cudaSuccess) return cuda_fail(e, "ntt_host H2D");
-    int rc = run(p, fwd, p->d_stage, batch, 0, p->L, nullptr);
-    if (rc) return rc;
-    if ((e = cudaMemcpyAsync(h, p->d_stage, bytes, cudaMemcpyDeviceToHost, 0)) != cudaSuccess) return cuda_fail(e, "ntt_host D2H");
-    if ((e = cudaStreamSynchronize(0)) != cudaSuccess) return cuda_fail(e, "ntt_host sync");
-    return MFHE_OK;
+    static cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+    if (!st[0])
+        for (int i = 0; i < 3; ++i)
+            if ((e = cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking)) != cudaSuccess) return cuda_fail(e, "ntt_host stream");
+    // ~32 MiB chunks, at least one poly, at most 64 chunks
+    size_t per = std::max<size_t>(1, ((size_t)32 << 20) / (poly_words * 8));
+    if ((batch + per - 1) / per > 64) per = (batch + 63) / 64;
+    const size_t nchunks = (batch + per - 1) / per;
+    std::vector<cudaEvent_t> up(nchunks), done(nchunks);
+    int rc = MFHE_OK;
+    for (size_t c = 0; c < nchunks; ++c) { cudaEventCreateWithFlags(&up[c], cudaEventDisableTiming); cudaEventCreateWithFlags(&done[c], cudaEventDisableTiming); }
+    for (size_t c = 0; c < nchunks && rc == MFHE_OK; ++c) {
+        const size_t b0 = c * per, nb = std::min(per, batch - b0), off = b0 * poly_words;
+        if ((e = cudaMemcpyAsync(p->d_stage + off, h + off, nb * poly_words * 8, cudaMemcpyHostToDevice, st[0])) != cudaSuccess) { rc = cuda_fail(e, "ntt_host H2D"); break; }
+        cudaEventRecord(up[c], st[0]);
+        cudaStreamWaitEvent(st[1], up[c], 0);
+        rc = run(p, fwd, p->d_stage + off, nb, 0, p->L, st[1]);
+        if (rc) break;
+        cudaEventRecord(done[c], st[1]);
+        cudaStreamWaitEvent(st[2], done[c], 0);
+        if ((e = cudaMemcpyAsync(h + off, p->d_stage + off, nb * poly_words * 8, cudaMemcpyDeviceToHost, st[2])) != cudaSuccess) rc = cuda_fail(e, "ntt_host D2H");
+    }
+    for (int i = 0; i < 3; ++i)
+        if ((e = cudaStreamSynchronize(st[i])) != cudaSuccess && rc == MFHE_OK) rc = cuda_fail(e, "ntt_host sync");
+    for (size_t c = 0; c < nchunks; ++c) { cudaEventDestroy(up[c]); cudaEventDestroy(done[c]); }
+    return rc;
 }
 extern "C" int mfhe_ntt_forward_host(mfhe_ntt_plan* p, uint64_t* h, size_t batch) { return run_host(p, true, h, batch); }
 extern "C" int mfhe_ntt_inverse_host(mfhe_ntt_plan* p, uint64_t* h, size_t batch) { return run_host(p, false, h, batch); }

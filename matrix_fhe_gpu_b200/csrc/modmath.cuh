@@ -41,20 +41,49 @@ __device__ __forceinline__ void reduce_bound(u64& x, u64 q) {
     if constexpr (B > 1 && T <= 1) x = csub(x, q);
 }
 
+// x * w mod q with an APPROXIMATE Shoup quotient: any 64-bit x, result in [0, 4q).
+// Qhat = x1*s1 + hi32(x1*s0) + hi32(x0*s1) drops x0*s0 and the carries of the two cross terms, so it is
+// within 2 of floor(x*w'/2^64); the remainder x*w - Qhat*q is formed mod 2^64 as x*w + Qhat*(-q) with the
+// product-accumulate chain below: 3 IMAD.WIDE + 2 IMAD.HI + 4 IMAD and two carry adds, against
+// 6 IMAD.WIDE + 4 IMAD + ~9 adds for the exact form (measured with cuobjdump, profiles/microbench).
+__device__ __forceinline__ u64 mul_shoup_lazy4(u64 x, tw_t w, u64 nq) {
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32), s0 = (u32)w.y, s1 = (u32)(w.y >> 32);
+    const u32 w0 = (u32)w.x, w1 = (u32)(w.x >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32);
+    u32 h0, h1, ql, qh, t0, t1;
+    asm("mul.hi.u32 %0, %2, %3;\n\t"
+        "mul.hi.u32 %1, %4, %5;"
+        : "=r"(h0), "=r"(h1) : "r"(x1), "r"(s0), "r"(x0), "r"(s1));
+    asm("mad.lo.cc.u32 %0, %2, %3, %4;\n\t"
+        "madc.hi.u32 %1, %2, %3, 0;\n\t"
+        "add.cc.u32 %0, %0, %5;\n\t"
+        "addc.u32 %1, %1, 0;"
+        : "=r"(ql), "=r"(qh) : "r"(x1), "r"(s1), "r"(h0), "r"(h1));
+    asm("mul.lo.u32 %0, %2, %3;\n\t"
+        "mul.hi.u32 %1, %2, %3;\n\t"
+        "mad.lo.u32 %1, %2, %4, %1;\n\t"
+        "mad.lo.u32 %1, %5, %3, %1;\n\t"
+        "mad.lo.cc.u32 %0, %6, %7, %0;\n\t"
+        "madc.hi.u32 %1, %6, %7, %1;\n\t"
+        "mad.lo.u32 %1, %6, %8, %1;\n\t"
+        "mad.lo.u32 %1, %9, %7, %1;"
+        : "=&r"(t0), "=&r"(t1) : "r"(x0), "r"(w0), "r"(w1), "r"(x1), "r"(ql), "r"(n0), "r"(n1), "r"(qh));
+    return ((u64)t1 << 32) | t0;
+}
+
 // ---- lazy-bound schedule of the forward (Cooley-Tukey) network -------------
-// A CT butterfly  x' = x + w*y, y' = x + 2q - w*y  with w*y in [0,2q) raises the
-// bound of both outputs to bound(x) + 2 (in units of q) whatever y was, because
-// the Shoup product accepts any 64-bit y.  With q < 2^60 values may grow to 16q,
-// so x needs a conditional subtract only every fourth stage instead of every
-// stage (ph/include/butterfly.cuh:10-22 subtracts in every butterfly).
+// A CT butterfly  x' = x + t, y' = x + 4q - t  with t = w*y in [0,4q) (approximate quotient) raises the
+// bound of both outputs to bound(x) + 4 (in units of q) whatever y was, because the Shoup product accepts
+// any 64-bit y.  With q < 2^60 values may grow to 16q, so x needs a conditional subtract only every second
+// or third stage instead of every butterfly (ph/include/butterfly.cuh:10-22 subtracts in every butterfly).
+// The last stage uses the exact quotient (t < 2q) so that two conditional subtracts canonicalise.
 constexpr int kFwdInBound = 2;                       // inputs may be in [0, 2q)
 __host__ __device__ constexpr int fwd_xtarget(int B, int s, int logn) {
     if (s == logn - 1) return 2;                     // last stage: leave < 4q for the final csubs
-    return (B + 2 > 16) ? 8 : B;
+    return (B + 4 > 16) ? 8 : B;
 }
 __host__ __device__ constexpr int fwd_bound_before(int s, int logn) {
     int B = kFwdInBound;
-    for (int i = 0; i < s; ++i) B = fwd_xtarget(B, i, logn) + 2;
+    for (int i = 0; i < s; ++i) B = fwd_xtarget(B, i, logn) + 4;
     return B;
 }
 
@@ -64,16 +93,24 @@ __device__ __forceinline__ void ct_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
     constexpr int B = fwd_bound_before(S, LOGN);
     constexpr int T = fwd_xtarget(B, S, LOGN);
     reduce_bound<B, (T < B ? T : B)>(x, q);
-    u64 t = mul_shoup_lazy(y, w, q);
-    y = x + q2 - t;
-    x = x + t;
+    if constexpr (S == LOGN - 1) {
+        const u64 t = mul_shoup_lazy(y, w, q);
+        y = x + q2 - t;
+        x = x + t;
+    } else {
+        const u64 t = mul_shoup_lazy4(y, w, 0 - q);
+        y = x + 2 * q2 - t;
+        x = x + t;
+    }
 }
 
-// Inverse (Gentleman-Sande) butterfly; all values stay in [0, 2q).
+// Inverse (Gentleman-Sande) butterfly; all values stay in [0, 4q): the sum is folded once by 4q, the
+// product comes out of the approximate-quotient multiply below 4q.
 __device__ __forceinline__ void gs_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
-    u64 t = x + q2 - y;
-    x = csub(x + y, q2);
-    y = mul_shoup_lazy(t, w, q);
+    const u64 q4 = 2 * q2;
+    const u64 t = x + q4 - y;
+    x = csub(x + y, q4);
+    y = mul_shoup_lazy4(t, w, 0 - q);
 }
 
 // generic (non-constant multiplicand) product, Barrett on the 128-bit product.

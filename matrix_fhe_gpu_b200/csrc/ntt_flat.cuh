@@ -13,8 +13,9 @@
 //     warp-private, XOR-swizzled shared-memory tile, so the row kernel needs no
 //     block-level barrier at all;
 //   * twiddles are {w, w'} pairs fetched with one LDG.128 (rows: LDG.256 for two);
-//   * lazy arithmetic uses the 4 spare bits of q < 2^60: one conditional subtract
-//     per four forward stages (modmath.cuh) instead of one per butterfly;
+//   * lazy arithmetic uses the 4 spare bits of q < 2^60: the Shoup quotient is only
+//     approximated (3 wide multiplies instead of 6, result < 4q) and x is folded once
+//     per two or three forward stages (modmath.cuh) instead of in every butterfly;
 //   * results are stored with 256-bit stores.
 #pragma once
 #include "modmath.cuh"
@@ -81,10 +82,12 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[8], u32 g0, const tw_t* __rest
             for (int jl = 0; jl < (1 << tb); ++jl) {
                 const int jx = (jh << (tb + 1)) | jl;
                 const int jy = jx | (1 << tb);
-                gs_bfly(v[jx], v[jy], w, q, q2);
-                if (b == LOGN - 1) {            // fold N^-1 into the last stage, then canonicalise
-                    v[jx] = mul_shoup(v[jx], ninv, q);
-                    v[jy] = csub(v[jy], q);
+                if (b == LOGN - 1) {            // last stage: exact products, N^-1 folded in, canonical
+                    const u64 t = v[jx] + 2 * q2 - v[jy], sum = v[jx] + v[jy];
+                    v[jx] = mul_shoup(sum, ninv, q);
+                    v[jy] = mul_shoup(t, w, q);
+                } else {
+                    gs_bfly(v[jx], v[jy], w, q, q2);
                 }
             }
         }

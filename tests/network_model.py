@@ -14,13 +14,13 @@ K_FWD_IN_BOUND = 2
 def fwd_xtarget(B, s, logn):
     if s == logn - 1:
         return 2
-    return 8 if B + 2 > 16 else B
+    return 8 if B + 4 > 16 else B
 
 
 def fwd_bound_before(s, logn):
     B = K_FWD_IN_BOUND
     for i in range(s):
-        B = fwd_xtarget(B, i, logn) + 2
+        B = fwd_xtarget(B, i, logn) + 4
     return B
 
 
@@ -51,9 +51,10 @@ class Net:
                 if x >= k * q:
                     x -= k * q
         assert x < T * q
-        t = (y * w) % q            # lazy product is in [0,2q); canonical is fine for the model
-        t += 0
-        yo = x + 2 * q - t
+        # worst case of the lazy product: [0,4q) with the approximate quotient, [0,2q) in the last stage
+        k = 2 if s == self.logn - 1 else 4
+        t = (y * w) % q + (k - 1) * q
+        yo = x + k * q - ((y * w) % q)
         xo = x + t
         assert xo < 2 ** 64 and yo < 2 ** 64
         self.max_bound = max(self.max_bound, -(-max(xo, yo) // q))
@@ -61,11 +62,12 @@ class Net:
 
     def gs(self, x, y, w):
         q = self.q
-        t = x + 2 * q - y
+        assert x < 4 * q and y < 4 * q
+        t = x + 4 * q - y
         s = x + y
-        if s >= 2 * q:
-            s -= 2 * q
-        return s, (t * w) % q
+        if s >= 4 * q:
+            s -= 4 * q
+        return s, (t * w) % q + 3 * q          # worst case of the approximate-quotient product
 
     def fwd_pass(self, v, g0, GB, ACT):
         L = self.logn

@@ -33,7 +33,7 @@ def test_lazy_bound_schedule_never_overflows(logn):
     for s in range(logn):
         assert M.fwd_bound_before(s, logn) == B
         T = min(M.fwd_xtarget(B, s, logn), B)
-        B = T + 2
+        B = T + (2 if s == logn - 1 else 4)      # approximate quotient: t < 4q; exact (t < 2q) in the last stage
         assert B <= 16
     assert B <= 4      # the row kernel finishes with csub(2q), csub(q)
 
