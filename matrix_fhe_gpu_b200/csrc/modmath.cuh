@@ -70,6 +70,58 @@ __device__ __forceinline__ u64 mul_shoup_lazy4(u64 x, tw_t w, u64 nq) {
     return ((u64)t1 << 32) | t0;
 }
 
+// ---- FP64-assisted approximate quotient -----------------------------------------------------------
+// B200 measurements (profiles/microbench): IMAD.WIDE / IMAD.HI run at ~0.4x the rate of a 32-bit IMAD on
+// the fmaheavy pipe, which is the pipe that binds the NTT kernels, while DFMA issues at the IMAD rate on
+// its own pipe.  The two cross terms  (x1*s0 + x0*s1) >> 32  of the Shoup quotient only have to be right
+// to within a couple of units, so they are moved to the FP64 pipe:
+//   * x0, x1 enter as doubles without a conversion: the bit pattern {x_i, 0x43300000} IS 2^52 + x_i;
+//   * the twiddle's Shoup word is converted once per twiddle (two I2F on the otherwise idle XU pipe) and
+//     K = C - 2^52 (s0 + s1),  C = 1.5 * 2^84 - 2^32,  cancels the 2^52 offsets (exact: multiples of 2^32);
+//   * D = fma(m1, s0, fma(m0, s1, K)) = 1.5 * 2^84 + (x1 s0 + x0 s1) - 2^32 + eps, |eps| <= 2^32 (two
+//     roundings at ulp 2^32), so the LOW 52 bits of D's pattern hold c = ((x1 s0 + x0 s1) >> 32) - 1 +- 1
+//     -- never above the true value -- and its pattern is kFpqOff + c;
+//   * Q + kFpqOff = x1*s1 + D_bits is one IMAD.WIDE with D's registers as the addend, and the constant
+//     kFpqOff * (-q) is cancelled by seeding the remainder chain with  cneg = -(kFpqOff * (-q)) mod 2^64.
+// Q is in (rho - 4, rho] for rho = x*w/q, hence the product is in [0, 4q) exactly like mul_shoup_lazy4,
+// at 3 IMAD.WIDE + 4 IMAD + 2 DFMA (+2 register moves) instead of 3 IMAD.WIDE + 2 IMAD.HI + 4 IMAD + 2 adds.
+constexpr u64 kFpqOff = 0x4538000000000000ull;            // bit pattern of 1.5 * 2^84
+struct twf_t { u64 w; u32 s1; double s0d, s1d, k; };      // a twiddle prepared for mul_fpq
+__device__ __forceinline__ twf_t fpq_prep(tw_t t) {
+    twf_t r;
+    r.w = t.x; r.s1 = (u32)(t.y >> 32);
+    r.s0d = __uint2double_rn((u32)t.y);
+    r.s1d = __uint2double_rn(r.s1);
+    const double c = 29014219670751100192948224.0 - 4294967296.0;          // 1.5 * 2^84 - 2^32
+    r.k = fma(-4503599627370496.0, r.s0d, fma(-4503599627370496.0, r.s1d, c));
+    return r;
+}
+// cneg = -(kFpqOff * (0 - q)) mod 2^64 = kFpqOff * q mod 2^64
+__device__ __forceinline__ u64 fpq_cneg(u64 q) { return kFpqOff * q; }
+__device__ __forceinline__ u64 mul_fpq(u64 x, const twf_t& w, u64 nq, u64 cneg) {
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32);
+    const double m0 = __hiloint2double(0x43300000, (int)x0), m1 = __hiloint2double(0x43300000, (int)x1);
+    const double d = fma(m1, w.s0d, fma(m0, w.s1d, w.k));
+    const u32 d0 = (u32)__double2loint(d), d1 = (u32)__double2hiint(d);
+    const u32 w0 = (u32)w.w, w1 = (u32)(w.w >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32);
+    const u32 c0 = (u32)cneg, c1 = (u32)(cneg >> 32);
+    u32 ql, qh, t0, t1;
+    asm("mad.lo.cc.u32 %0, %2, %3, %4;\n\t"
+        "madc.hi.u32 %1, %2, %3, %5;"
+        : "=r"(ql), "=r"(qh) : "r"(x1), "r"(w.s1), "r"(d0), "r"(d1));
+    asm("mad.lo.cc.u32 %0, %2, %3, %10;\n\t"
+        "madc.hi.u32 %1, %2, %3, %11;\n\t"
+        "mad.lo.u32 %1, %2, %4, %1;\n\t"
+        "mad.lo.u32 %1, %5, %3, %1;\n\t"
+        "mad.lo.cc.u32 %0, %6, %7, %0;\n\t"
+        "madc.hi.u32 %1, %6, %7, %1;\n\t"
+        "mad.lo.u32 %1, %6, %8, %1;\n\t"
+        "mad.lo.u32 %1, %9, %7, %1;"
+        : "=&r"(t0), "=&r"(t1)
+        : "r"(x0), "r"(w0), "r"(w1), "r"(x1), "r"(ql), "r"(n0), "r"(n1), "r"(qh), "r"(c0), "r"(c1));
+    return ((u64)t1 << 32) | t0;
+}
+
 // ---- lazy-bound schedule of the forward (Cooley-Tukey) network -------------
 // A CT butterfly  x' = x + t, y' = x + 4q - t  with t = w*y in [0,4q) (approximate quotient) raises the
 // bound of both outputs to bound(x) + 4 (in units of q) whatever y was, because the Shoup product accepts

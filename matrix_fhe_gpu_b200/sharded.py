@@ -1,0 +1,112 @@
+"""Multi-GPU side of the hot path: one process per GPU, torch.distributed for the plumbing.
+
+Two cases exist on this path:
+
+* batch sharding (flat NTT, the matrix pipeline): every limb-poly / (re, im) pair is independent, so
+  rank r simply processes items r, r+k, ... -- `batch_slice` -- and there is NO data-path collective;
+* limb-sharded base conversion (BASELINE config 5): rank r owns a window of the input base Q and a
+  window of the output base P.  Base conversion needs every input limb of a coefficient, so this is
+  the one real exchange step.  Each rank forms the partial sums of ITS input limbs for ALL output
+  limbs (mfhe_bconv_partial: already reduced mod p_j, so partials add without overflow), the partials
+  are exchanged so that every rank receives the world's partials for ITS output limbs only
+  (`exchange_partials`: an all-to-all; (k-1)/k * batch * L_out * N * 8 bytes leave each rank instead
+  of the (k-1) * batch * L_in * N * 8 an all-gather of the inputs would move), and mfhe_bconv_reduce
+  adds them mod p_j.  The local INTT before and NTT after are Phantom's
+  nwt_2d_radix8_backward/forward_inplace on a limb window (ph/src/ntt/intt_2d.cu:724-757,
+  fntt_2d.cu:620-653); the conversion is DBaseConverter::bConv_BEHZ (ph/src/rns_bconv.cu:212-229).
+
+`limb_windows`, `batch_slice` and `exchange_partials` are pure torch / torch.distributed (they run on
+CPU tensors over gloo in the test-suite and on CUDA tensors over NCCL on the box); the compute calls
+go through the C ABI and need the GPU.
+"""
+from __future__ import annotations
+
+from typing import List, Sequence, Tuple
+
+
+def limb_windows(total: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous balanced windows (start, count) of `total` limbs over `world` ranks; the first
+    total % world ranks own one limb more.  Config 5: 48 Q-limbs over 8 ranks -> 6 each, 16 P-limbs -> 2."""
+    if world < 1 or total < 0:
+        raise ValueError("bad partition")
+    base, extra = divmod(total, world)
+    out, start = [], 0
+    for r in range(world):
+        cnt = base + (1 if r < extra else 0)
+        out.append((start, cnt))
+        start += cnt
+    return out
+
+
+def batch_slice(batch: int, rank: int, world: int) -> range:
+    """Items of a batch owned by `rank`: r, r + world, ... (pairs r, r+k, ...)."""
+    return range(rank, batch, world)
+
+
+def pack_for_exchange(partial, out_windows: Sequence[Tuple[int, int]]):
+    """partial [batch][L_out][N] -> flat send buffer ordered by destination rank, each chunk
+    [batch][count_r][N]; returns (send, split_sizes)."""
+    import torch
+    chunks = [partial[:, s:s + c, :].reshape(-1) for s, c in out_windows]
+    return torch.cat(chunks), [int(ch.numel()) for ch in chunks]
+
+
+def exchange_partials(partial, out_windows: Sequence[Tuple[int, int]], rank: int, world: int, group=None):
+    """All-to-all of the base-conversion partial sums.
+
+    partial: [batch][L_out][N] int64 (u64 bit patterns) on this rank.
+    Returns parts [world][batch][count_rank][N]: every rank's partial for THIS rank's output window,
+    in rank order -- the layout mfhe_bconv_reduce consumes."""
+    import torch
+    import torch.distributed as dist
+    batch, _, n = partial.shape
+    send, in_splits = pack_for_exchange(partial, out_windows)
+    mine = out_windows[rank][1]
+    recv = torch.empty(world * batch * mine * n, dtype=partial.dtype, device=partial.device)
+    if world == 1:
+        recv.copy_(send)
+    else:
+        dist.all_to_all_single(recv, send, output_split_sizes=[batch * mine * n] * world,
+                               input_split_sizes=in_splits, group=group)
+    return recv.view(world, batch, mine, n)
+
+
+def emulate_exchange(partials, out_windows: Sequence[Tuple[int, int]], rank: int):
+    """Single-process stand-in for exchange_partials: partials[r] is rank r's [batch][L_out][N]."""
+    import torch
+    s, c = out_windows[rank]
+    return torch.stack([p[:, s:s + c, :] for p in partials]).contiguous()
+
+
+class LimbShardedBconv:
+    """Config 5 step on one rank: INTT(own Q-limbs) -> partial base conversion -> exchange -> reduce
+    -> NTT(own P-limbs).  x_local is [batch][q_count][N] in NTT form; the result is [batch][p_count][N]."""
+
+    def __init__(self, logn: int, q_in, p_out, rank: int, world: int, group=None):
+        from . import NttPlan
+        from .scheme import BconvPlan
+        self.logn, self.n = logn, 1 << logn
+        self.rank, self.world, self.group = rank, world, group
+        self.q = [int(v) for v in q_in]
+        self.p = [int(v) for v in p_out]
+        self.q_windows = limb_windows(len(self.q), world)
+        self.p_windows = limb_windows(len(self.p), world)
+        self.plan_q = NttPlan(logn, self.q)
+        self.plan_p = NttPlan(logn, self.p)
+        self.bconv = BconvPlan(self.q, self.p)
+
+    def local_partial(self, x_local, batch: int, rank: int | None = None):
+        qs, qc = self.q_windows[self.rank if rank is None else rank]
+        self.plan_q.inverse_limbs_(x_local, qs, qc)
+        return self.bconv.partial(x_local, qs, qc, self.n, batch).view(batch, len(self.p), self.n)
+
+    def finish(self, parts, batch: int, rank: int | None = None):
+        ps, pc = self.p_windows[self.rank if rank is None else rank]
+        out = self.bconv.reduce(parts.reshape(-1), parts.shape[0], ps, pc, self.n, batch)
+        self.plan_p.forward_limbs_(out, ps, pc)
+        return out.view(batch, pc, self.n)
+
+    def step(self, x_local, batch: int):
+        partial = self.local_partial(x_local, batch)
+        parts = exchange_partials(partial, self.p_windows, self.rank, self.world, self.group)
+        return self.finish(parts, batch)

@@ -1,0 +1,119 @@
+"""World-size-2 gloo tests of the multi-GPU host logic: limb windows, batch slices and the
+all-to-all of base-conversion partial sums.  The partial sums themselves are formed here with Python
+integers (the kernels need a GPU); the result is checked against the oracle's full base conversion."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle as O
+from matrix_fhe_gpu_b200 import sharded as S
+
+
+def test_limb_windows_cover_and_balance():
+    assert S.limb_windows(48, 8) == [(6 * r, 6) for r in range(8)]
+    assert S.limb_windows(16, 8) == [(2 * r, 2) for r in range(8)]
+    for total in (1, 5, 7, 48):
+        for world in (1, 2, 3, 8):
+            w = S.limb_windows(total, world)
+            assert sum(c for _, c in w) == total
+            assert all(w[i][0] + w[i][1] == w[i + 1][0] for i in range(world - 1))
+            assert max(c for _, c in w) - min(c for _, c in w) <= 1
+
+
+def test_batch_slice_partitions():
+    for batch in (1, 7, 128):
+        for world in (1, 2, 4, 8):
+            seen = sorted(i for r in range(world) for i in S.batch_slice(batch, r, world))
+            assert seen == list(range(batch))
+
+
+def _py_partial(x, q, p, window):
+    """sum over input limbs in `window` of y_i * (Q/q_i mod p_j) mod p_j with Python integers; x [L_in][N]."""
+    qs = [int(v) for v in q]; ps = [int(v) for v in p]
+    Q = 1
+    for v in qs:
+        Q *= v
+    N = x.shape[1]
+    out = np.zeros((len(ps), N), dtype=np.uint64)
+    s, c = window
+    for j, pj in enumerate(ps):
+        acc = [0] * N
+        for i in range(s, s + c):
+            qh = Q // qs[i]
+            inv = pow(qh % qs[i], -1, qs[i])
+            f = qh % pj
+            for d in range(N):
+                acc[d] = (acc[d] + (int(x[i, d]) * inv % qs[i]) * f) % pj
+        out[j] = np.array(acc, dtype=np.uint64)
+    return out
+
+
+def _worker(rank, world, port, q, p, x, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        batch = x.shape[0]
+        qwin = S.limb_windows(len(q), world)
+        pwin = S.limb_windows(len(p), world)
+        partial = np.stack([_py_partial(x[b], q, p, qwin[rank]) for b in range(batch)])
+        t = torch.from_numpy(partial.view(np.int64))
+        parts = S.exchange_partials(t, pwin, rank, world)
+        assert tuple(parts.shape) == (world, batch, pwin[rank][1], x.shape[2])
+        arr = parts.numpy().view(np.uint64)
+        ps, pc = pwin[rank]
+        out = np.zeros((batch, pc, x.shape[2]), dtype=np.uint64)
+        for j in range(pc):
+            pj = int(p[ps + j])
+            acc = np.zeros((batch, x.shape[2]), dtype=object)
+            for r in range(world):
+                acc = acc + arr[r, :, j, :].astype(object)
+            out[:, j, :] = (acc % pj).astype(np.uint64)
+        ret[rank] = out
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+@pytest.mark.parametrize("l_in,l_out", [(4, 3), (5, 2)])
+def test_exchange_partials_gloo_world2(l_in, l_out):
+    world, N, batch = 2, 32, 2
+    primes = O.get_primes(2 * N, 40, l_in + l_out)
+    q, p = primes[:l_in], primes[l_in:]
+    x = O.synth_polys(5, batch, q, N)
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_worker, args=(world, _free_port(), q, p, x, ret), nprocs=world, join=True)
+        pwin = S.limb_windows(l_out, world)
+        for b in range(batch):
+            want = O.bconv(x[b], q, p)
+            for r in range(world):
+                s, c = pwin[r]
+                assert (ret[r][b] == want[s:s + c]).all()
+
+
+def test_emulate_exchange_matches_pack():
+    world, batch, l_out, N = 3, 2, 5, 8
+    win = S.limb_windows(l_out, world)
+    partials = [torch.arange(batch * l_out * N, dtype=torch.int64).view(batch, l_out, N) + 1000 * r for r in range(world)]
+    for r in range(world):
+        parts = S.emulate_exchange(partials, win, r)
+        s, c = win[r]
+        for src in range(world):
+            assert torch.equal(parts[src], partials[src][:, s:s + c, :])
+        send, splits = S.pack_for_exchange(partials[r], win)
+        assert splits == [batch * cc * N for _, cc in win]
+        off = sum(splits[:r])
+        assert torch.equal(send[off:off + splits[r]].view(batch, c, N), partials[r][:, s:s + c, :])
