@@ -8,7 +8,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libmfhe_b200.so")
+LIB = os.environ.get("MFHE_LIB_PATH") or os.path.join(HERE, "libmfhe_b200.so")     # override: A/B experiments only
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
@@ -41,7 +41,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objs = []
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")] + os.environ.get("MFHE_NVCC_EXTRA", "").split()
+    if os.environ.get("MFHE_LIB_PATH"):
+        objdir = objdir + "_" + os.path.basename(LIB)
+        os.makedirs(objdir, exist_ok=True)
     procs = []
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")

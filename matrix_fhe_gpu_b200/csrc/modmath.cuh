@@ -86,6 +86,19 @@ __device__ __forceinline__ u64 mul_shoup_lazy4(u64 x, tw_t w, u64 nq) {
 // Q is in (rho - 4, rho] for rho = x*w/q, hence the product is in [0, 4q) exactly like mul_shoup_lazy4,
 // at 3 IMAD.WIDE + 4 IMAD + 2 DFMA (+2 register moves) instead of 3 IMAD.WIDE + 2 IMAD.HI + 4 IMAD + 2 adds.
 constexpr u64 kFpqOff = 0x4538000000000000ull;            // bit pattern of 1.5 * 2^84
+#ifndef MFHE_FPQ_MODE
+#define MFHE_FPQ_MODE 0      // how x0, x1 become doubles: 0 = {x_i, 0x43300000} register pairs, 1 = I2F (XU pipe), 2 = PRMT copies
+#endif
+#ifndef MFHE_MODMUL
+#define MFHE_MODMUL 1      // butterfly product: 0 = FP64-assisted quotient, 1 = integer-only approximate quotient (mul_shoup_lazy4).
+                           // In isolation 0 is 9-18 % faster (profiles/r1_04_intpipe.log); inside the NTT kernels its extra live
+                           // registers (prepared twiddle = 9 words) cost occupancy or spills and it measured SLOWER
+                           // (profiles/r1_06_ntt_ab.txt), so 1 is the default.
+#endif
+#if MFHE_MODMUL == 1
+struct twf_t { tw_t t; };
+__device__ __forceinline__ twf_t fpq_prep(tw_t t) { return twf_t{t}; }
+#else
 struct twf_t { u64 w; u32 s1; double s0d, s1d, k; };      // a twiddle prepared for mul_fpq
 __device__ __forceinline__ twf_t fpq_prep(tw_t t) {
     twf_t r;
@@ -93,15 +106,33 @@ __device__ __forceinline__ twf_t fpq_prep(tw_t t) {
     r.s0d = __uint2double_rn((u32)t.y);
     r.s1d = __uint2double_rn(r.s1);
     const double c = 29014219670751100192948224.0 - 4294967296.0;          // 1.5 * 2^84 - 2^32
+#if MFHE_FPQ_MODE == 1
+    r.k = c;                                             // true conversions of x0, x1: no 2^52 offsets to cancel
+#else
     r.k = fma(-4503599627370496.0, r.s0d, fma(-4503599627370496.0, r.s1d, c));
+#endif
     return r;
 }
+#endif
 // cneg = -(kFpqOff * (0 - q)) mod 2^64 = kFpqOff * q mod 2^64
 __device__ __forceinline__ u64 fpq_cneg(u64 q) { return kFpqOff * q; }
+#if MFHE_MODMUL == 1
+__device__ __forceinline__ u64 mul_fpq(u64 x, const twf_t& w, u64 nq, u64) { return mul_shoup_lazy4(x, w.t, nq); }
+#else
 __device__ __forceinline__ u64 mul_fpq(u64 x, const twf_t& w, u64 nq, u64 cneg) {
     const u32 x0 = (u32)x, x1 = (u32)(x >> 32);
+#if MFHE_FPQ_MODE == 1
+    const double d = fma(__uint2double_rn(x1), w.s0d, fma(__uint2double_rn(x0), w.s1d, w.k));
+#elif MFHE_FPQ_MODE == 2
+    u32 a0, a1;
+    asm("prmt.b32 %0, %1, %1, 0x3210;" : "=r"(a0) : "r"(x0));
+    asm("prmt.b32 %0, %1, %1, 0x3210;" : "=r"(a1) : "r"(x1));
+    const double m0 = __hiloint2double(0x43300000, (int)a0), m1 = __hiloint2double(0x43300000, (int)a1);
+    const double d = fma(m1, w.s0d, fma(m0, w.s1d, w.k));
+#else
     const double m0 = __hiloint2double(0x43300000, (int)x0), m1 = __hiloint2double(0x43300000, (int)x1);
     const double d = fma(m1, w.s0d, fma(m0, w.s1d, w.k));
+#endif
     const u32 d0 = (u32)__double2loint(d), d1 = (u32)__double2hiint(d);
     const u32 w0 = (u32)w.w, w1 = (u32)(w.w >> 32), n0 = (u32)nq, n1 = (u32)(nq >> 32);
     const u32 c0 = (u32)cneg, c1 = (u32)(cneg >> 32);
@@ -121,6 +152,7 @@ __device__ __forceinline__ u64 mul_fpq(u64 x, const twf_t& w, u64 nq, u64 cneg) 
         : "r"(x0), "r"(w0), "r"(w1), "r"(x1), "r"(ql), "r"(n0), "r"(n1), "r"(qh), "r"(c0), "r"(c1));
     return ((u64)t1 << 32) | t0;
 }
+#endif
 
 // ---- lazy-bound schedule of the forward (Cooley-Tukey) network -------------
 // A CT butterfly  x' = x + t, y' = x + 4q - t  with t = w*y in [0,4q) (approximate quotient) raises the
@@ -139,30 +171,34 @@ __host__ __device__ constexpr int fwd_bound_before(int s, int logn) {
     return B;
 }
 
-// Forward butterfly at global stage S of a 2^LOGN transform.
+// Forward butterfly at global stage S of a 2^LOGN transform.  `w` is the prepared twiddle (FP64-assisted
+// quotient); the last stage takes the raw {w, w'} pair and the exact quotient so that two conditional
+// subtracts canonicalise the outputs.
+struct qconst_t { u64 q, q2, q4, nq, cneg; };
+__device__ __forceinline__ qconst_t make_qconst(u64 q) { return qconst_t{q, 2 * q, 4 * q, 0 - q, fpq_cneg(q)}; }
+
 template <int LOGN, int S>
-__device__ __forceinline__ void ct_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
+__device__ __forceinline__ void ct_bfly(u64& x, u64& y, const twf_t& w, tw_t raw, const qconst_t& c) {
     constexpr int B = fwd_bound_before(S, LOGN);
     constexpr int T = fwd_xtarget(B, S, LOGN);
-    reduce_bound<B, (T < B ? T : B)>(x, q);
+    reduce_bound<B, (T < B ? T : B)>(x, c.q);
     if constexpr (S == LOGN - 1) {
-        const u64 t = mul_shoup_lazy(y, w, q);
-        y = x + q2 - t;
+        const u64 t = mul_shoup_lazy(y, raw, c.q);
+        y = x + c.q2 - t;
         x = x + t;
     } else {
-        const u64 t = mul_shoup_lazy4(y, w, 0 - q);
-        y = x + 2 * q2 - t;
+        const u64 t = mul_fpq(y, w, c.nq, c.cneg);
+        y = x + c.q4 - t;
         x = x + t;
     }
 }
 
 // Inverse (Gentleman-Sande) butterfly; all values stay in [0, 4q): the sum is folded once by 4q, the
 // product comes out of the approximate-quotient multiply below 4q.
-__device__ __forceinline__ void gs_bfly(u64& x, u64& y, tw_t w, u64 q, u64 q2) {
-    const u64 q4 = 2 * q2;
-    const u64 t = x + q4 - y;
-    x = csub(x + y, q4);
-    y = mul_shoup_lazy4(t, w, 0 - q);
+__device__ __forceinline__ void gs_bfly(u64& x, u64& y, const twf_t& w, const qconst_t& c) {
+    const u64 t = x + c.q4 - y;
+    x = csub(x + y, c.q4);
+    y = mul_fpq(t, w, c.nq, c.cneg);
 }
 
 // generic (non-constant multiplicand) product, Barrett on the 128-bit product.

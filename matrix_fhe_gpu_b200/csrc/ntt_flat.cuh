@@ -14,8 +14,11 @@
 //     block-level barrier at all;
 //   * twiddles are {w, w'} pairs fetched with one LDG.128 (rows: LDG.256 for two);
 //   * lazy arithmetic uses the 4 spare bits of q < 2^60: the Shoup quotient is only
-//     approximated (3 wide multiplies instead of 6, result < 4q) and x is folded once
-//     per two or three forward stages (modmath.cuh) instead of in every butterfly;
+//     approximated -- its cross terms come from two DFMAs on the FP64 pipe, leaving 3 IMAD.WIDE
+//     + 4 IMAD on the binding fmaheavy pipe, result < 4q -- and x is folded once per two or
+//     three forward stages (modmath.cuh) instead of in every butterfly;
+//   * every thread works on the same positions of PB polys of the batch, so each twiddle
+//     is fetched and prepared once per PB butterflies;
 //   * results are stored with 256-bit stores.
 #pragma once
 #include "modmath.cuh"
@@ -34,16 +37,19 @@ struct NttTables {            // device pointers, per plan
 
 // ---------------------------------------------------------------------------
 // One in-register radix-8 pass over three consecutive bits [P+2..P] of the
-// sub-transform index.  v[j] holds the element whose triple equals j.
+// sub-transform index, applied to PB polys of the same limb at once: the
+// twiddle of a butterfly depends only on its position, so it is fetched (one
+// LDG.128) and prepared for the FP64-assisted quotient (fpq_prep) ONCE and used
+// for the PB polys.  v[p][j] holds the element of poly p whose triple equals j.
 //   LOGN  size of the whole transform
 //   GB    global bit position of triple bit 0
 //   ACT   bit mask of the triple bits that are transformed in this pass
-//   g0    global coefficient index of v[0]
+//   g0    global coefficient index of v[.][0]
 // Stage for global bit b: s = LOGN-1-b, twiddle index 2^s + (g >> (b+1)).
 // ---------------------------------------------------------------------------
-template <int LOGN, int GB, int ACT>
-__device__ __forceinline__ void fwd_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ tw,
-                                         u64 q, u64 q2) {
+template <int LOGN, int GB, int ACT, int PB>
+__device__ __forceinline__ void fwd_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __restrict__ tw,
+                                         const qconst_t& c) {
 #pragma unroll
     for (int tb = 2; tb >= 0; --tb) {
         if (!((ACT >> tb) & 1)) continue;
@@ -52,23 +58,27 @@ __device__ __forceinline__ void fwd_pass(u64 (&v)[8], u32 g0, const tw_t* __rest
         const u32 base = (1u << s) + (g0 >> (b + 1));
 #pragma unroll
         for (int jh = 0; jh < (4 >> tb); ++jh) {
-            const tw_t w = __ldg(tw + base + jh);
+            const tw_t raw = __ldg(tw + base + jh);
+            twf_t w;
+            if (s != LOGN - 1) w = fpq_prep(raw);
 #pragma unroll
-            for (int jl = 0; jl < (1 << tb); ++jl) {
-                const int jx = (jh << (tb + 1)) | jl;
-                // stage number must be a constant expression for the bound schedule
-                if (tb == 2) ct_bfly<LOGN, LOGN - 1 - (GB + 2)>(v[jx], v[jx | 4], w, q, q2);
-                if (tb == 1) ct_bfly<LOGN, LOGN - 1 - (GB + 1)>(v[jx], v[jx | 2], w, q, q2);
-                if (tb == 0) ct_bfly<LOGN, LOGN - 1 - (GB + 0)>(v[jx], v[jx | 1], w, q, q2);
+            for (int p = 0; p < PB; ++p) {
+#pragma unroll
+                for (int jl = 0; jl < (1 << tb); ++jl) {
+                    const int jx = (jh << (tb + 1)) | jl;
+                    // stage number must be a constant expression for the bound schedule
+                    if (tb == 2) ct_bfly<LOGN, LOGN - 1 - (GB + 2)>(v[p][jx], v[p][jx | 4], w, raw, c);
+                    if (tb == 1) ct_bfly<LOGN, LOGN - 1 - (GB + 1)>(v[p][jx], v[p][jx | 2], w, raw, c);
+                    if (tb == 0) ct_bfly<LOGN, LOGN - 1 - (GB + 0)>(v[p][jx], v[p][jx | 1], w, raw, c);
+                }
             }
         }
-        (void)s;
     }
 }
 
-template <int LOGN, int GB, int ACT>
-__device__ __forceinline__ void inv_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ itw,
-                                         u64 q, u64 q2, tw_t ninv, tw_t w1n) {
+template <int LOGN, int GB, int ACT, int PB>
+__device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __restrict__ itw,
+                                         const qconst_t& c, tw_t ninv, tw_t w1n) {
 #pragma unroll
     for (int tb = 0; tb <= 2; ++tb) {
         if (!((ACT >> tb) & 1)) continue;
@@ -77,21 +87,38 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[8], u32 g0, const tw_t* __rest
         const u32 base = (1u << s) + (g0 >> (b + 1));
 #pragma unroll
         for (int jh = 0; jh < (4 >> tb); ++jh) {
-            tw_t w = (b == LOGN - 1) ? w1n : __ldg(itw + base + jh);
+            twf_t w;
+            if (b != LOGN - 1) w = fpq_prep(__ldg(itw + base + jh));
 #pragma unroll
-            for (int jl = 0; jl < (1 << tb); ++jl) {
-                const int jx = (jh << (tb + 1)) | jl;
-                const int jy = jx | (1 << tb);
-                if (b == LOGN - 1) {            // last stage: exact products, N^-1 folded in, canonical
-                    const u64 t = v[jx] + 2 * q2 - v[jy], sum = v[jx] + v[jy];
-                    v[jx] = mul_shoup(sum, ninv, q);
-                    v[jy] = mul_shoup(t, w, q);
-                } else {
-                    gs_bfly(v[jx], v[jy], w, q, q2);
+            for (int p = 0; p < PB; ++p) {
+#pragma unroll
+                for (int jl = 0; jl < (1 << tb); ++jl) {
+                    const int jx = (jh << (tb + 1)) | jl;
+                    const int jy = jx | (1 << tb);
+                    if (b == LOGN - 1) {        // last stage: exact products, N^-1 folded in, canonical
+                        const u64 t = v[p][jx] + c.q4 - v[p][jy], sum = v[p][jx] + v[p][jy];
+                        v[p][jx] = mul_shoup(sum, ninv, c.q);
+                        v[p][jy] = mul_shoup(t, w1n, c.q);
+                    } else {
+                        gs_bfly(v[p][jx], v[p][jy], w, c);
+                    }
                 }
             }
         }
     }
+}
+
+// single-poly forms used by the n-point networks (ntt_small.cuh, scheme.cu)
+template <int LOGN, int GB, int ACT>
+__device__ __forceinline__ void fwd_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ tw, u64 q, u64 /*q2*/) {
+    const qconst_t c = make_qconst(q);
+    fwd_pass<LOGN, GB, ACT, 1>(reinterpret_cast<u64 (&)[1][8]>(v), g0, tw, c);
+}
+template <int LOGN, int GB, int ACT>
+__device__ __forceinline__ void inv_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ itw, u64 q, u64 /*q2*/,
+                                         tw_t ninv, tw_t w1n) {
+    const qconst_t c = make_qconst(q);
+    inv_pass<LOGN, GB, ACT, 1>(reinterpret_cast<u64 (&)[1][8]>(v), g0, itw, c, ninv, w1n);
 }
 
 // position of element j of a thread whose remaining index bits are u, triple at P
