@@ -36,6 +36,7 @@ WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
     a.moduli = c->d_moduli; a.mu = c->d_mu;
     a.n = c->n; a.cols = c->n * c->n; a.limbs = c->L; a.phi = c->phi;
     a.split = c->wsplit; a.delta = c->delta;
+    a.tabd = inverse ? c->d_wdig_inv : c->d_wdig_fwd; a.h_ndig = c->ndig.data();
     return a;
 }
 
@@ -43,7 +44,7 @@ WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
 
 extern "C" void mfhe_ctx_destroy(mfhe_ctx* c) {
     if (!c) return;
-    cudaFree(c->d_moduli); cudaFree(c->d_mu); cudaFree(c->d_wtab_fwd); cudaFree(c->d_wtab_inv);
+    cudaFree(c->d_moduli); cudaFree(c->d_mu); cudaFree(c->d_wtab_fwd); cudaFree(c->d_wtab_inv); cudaFree(c->d_wdig_fwd); cudaFree(c->d_wdig_inv);
     cudaFree(c->d_wdft_fwd); cudaFree(c->d_wdft_inv);
     cudaFree(c->d_xyV); cudaFree(c->d_xyVT); cudaFree(c->d_xyVinv); cudaFree(c->d_xyVinvT);
     cudaFree(c->d_crt_Q); cudaFree(c->d_crt_Qhalf); cudaFree(c->d_crt_M); cudaFree(c->d_crt_inv);
@@ -71,6 +72,9 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     const size_t phi = (size_t)c->phi, pp = phi * phi;
     std::vector<uint64_t> tab_fwd((size_t)L * pp), tab_inv((size_t)L * pp);
     std::vector<host::TwPair> mu(L);
+    const bool want_digits = (phi % 64 == 0);               // the tensor-core W-CRT tiling (wcrt_tc.cu)
+    std::vector<unsigned char> dig_fwd(want_digits ? (size_t)L * 8 * pp : 0), dig_inv(dig_fwd.size());
+    c->ndig.assign(L, 8);
     std::vector<host::cplx> wV, wVinv, xV, xVinv;
     host::CrtTables crt;
     try {
@@ -104,6 +108,13 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
                     tab_fwd[(size_t)l * pp + i * phi + o] = pack(V[o * phi + i]);
                     tab_inv[(size_t)l * pp + i * phi + o] = pack(Vinv[o * phi + i]);
                 }
+            { int bits = 0; while (bits < 64 && (q >> bits)) ++bits; c->ndig[l] = (bits + 7) / 8; }
+            if (want_digits)
+                for (int u = 0; u < 8; ++u)
+                    for (size_t k = 0; k < pp; ++k) {
+                        dig_fwd[((size_t)l * 8 + u) * pp + k] = (unsigned char)(V[k] >> (8 * u));
+                        dig_inv[((size_t)l * 8 + u) * pp + k] = (unsigned char)(Vinv[k] >> (8 * u));
+                    }
             const unsigned __int128 m = ~(unsigned __int128)0 / q;
             mu[l] = host::TwPair{(uint64_t)m, (uint64_t)(m >> 64)};
         }
@@ -130,6 +141,7 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
 #define UP(dst, vec) if (e == cudaSuccess) e = upload(dst, (vec).data(), (vec).size() * sizeof((vec)[0]))
     UP(c->d_moduli, c->moduli); UP(c->d_mu, mu); UP(c->d_wtab_fwd, tab_fwd); UP(c->d_wtab_inv, tab_inv);
     UP(c->d_wdft_fwd, wf); UP(c->d_wdft_inv, wi);
+    if (want_digits) { UP(c->d_wdig_fwd, dig_fwd); UP(c->d_wdig_inv, dig_inv); }
     UP(c->d_xyV, xV); UP(c->d_xyVT, xVT); UP(c->d_xyVinv, xVinv); UP(c->d_xyVinvT, xVinvT);
     UP(c->d_crt_Q, crt.Q); UP(c->d_crt_Qhalf, crt.Qhalf); UP(c->d_crt_M, crt.M); UP(c->d_crt_inv, crt.inv);
 #undef UP

@@ -22,6 +22,9 @@ struct mfhe_ctx {
     mfhe::u64* d_wtab_fwd = nullptr;          // [L][i = W-coeff r][o = lane w]   (transposed for the GEMM)
     mfhe::u64* d_wtab_inv = nullptr;          // [L][i = lane w][o = W-coeff r]
     int wsplit = 0;                           // 1: tables stored as {lo26, hi} pairs (all q < 2^52)
+    unsigned char* d_wdig_fwd = nullptr;      // [L][8 digits][o][i] bytes: the same tables cut into 8-bit digits,
+    unsigned char* d_wdig_inv = nullptr;      //   K-major, for the tensor-core W-CRT (wcrt_tc.cu)
+    std::vector<int> ndig;                    // [L] ceil(bits(q_l) / 8)
     double2* d_wdft_fwd = nullptr;            // [i = r][o = w]
     double2* d_wdft_inv = nullptr;            // [i = w][o = r]
     double2 *d_xyV = nullptr, *d_xyVT = nullptr, *d_xyVinv = nullptr, *d_xyVinvT = nullptr;   // [n][n]
@@ -60,6 +63,9 @@ struct WcrtArgs {
     int source = kSrcMem;
     int split = 0;
     double delta = 0;
+    const unsigned char* tabd = nullptr;   // digit tables [limbs][8][phi][phi] (tensor-core path), may be null
+    const int* h_ndig = nullptr;           // HOST array [limbs]: 8-bit digits per modulus
+    int lz0 = 0, lzn = 0;                  // relative limb window of one launch (set by wcrt_launch)
 };
 cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st);
 

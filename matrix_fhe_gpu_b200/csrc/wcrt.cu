@@ -19,40 +19,14 @@
 //     input and the quantiser (llround(z * delta) mod q) feed the GEMM without a round trip through
 //     HBM, and the epilogue writes either layout (and an optional second copy) directly.
 #include "ctx.h"
+#include "wcrt_common.cuh"
+
+#include <cstdlib>
 
 namespace mfhe {
 
 constexpr int TO = 64, TC = 64, TK = 16, WTHREADS = 256;
 constexpr u32 MASK26 = (1u << 26) - 1u;
-
-__device__ __forceinline__ size_t poly_set_addr(int layout, int w, int l, int c, int n, int cols, int L) {
-    if (layout == MFHE_LAYOUT_POLY) {
-        const int y = c / n, x = c - y * n;
-        return (((size_t)w * n + y) * L + l) * n + x;
-    }
-    return ((size_t)w * L + l) * cols + c;
-}
-
-__device__ __forceinline__ u64 splitmix64_dev(u64 x) {
-    x += 0x9E3779B97F4A7C15ULL;
-    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
-    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
-    return x ^ (x >> 31);
-}
-// src/core/HE.cu:590-627: one centred integer per logical coefficient [w][pos], same in every limb
-__device__ __forceinline__ long long gaussian_noise_value(u64 coeff_id) {
-    const u64 r1 = splitmix64_dev(0xD6E8FEB86659FD93ULL ^ coeff_id), r2 = splitmix64_dev(r1);
-    const double inv53 = 1.0 / 9007199254740992.0;
-    const double u1 = ((double)(r1 >> 11) + 1.0) * inv53, u2 = ((double)(r2 >> 11) + 1.0) * inv53;
-    const double mag = 3.2 * sqrt(-2.0 * log(u1));
-    return llround(mag * cos(6.283185307179586 * u2));
-}
-// src/core/HE.cu:564-578
-__device__ __forceinline__ u64 uniform_value(u64 idx, u64 q, u64 mu_hi) {
-    u64 seed = 123456789ULL + idx;
-    seed = seed * 6364136223846793005ULL + 1442695040888963407ULL;
-    return reduce64(seed, q, mu_hi);
-}
 
 // four consecutive columns of input row i, as canonical residues
 template <int SRC>
@@ -92,7 +66,7 @@ wcrt_gemm_kernel(const WcrtArgs a) {
     __shared__ __align__(16) u64 sTab[2][TK][TO];
     __shared__ __align__(16) u64 sIn[2][TK][TC];
     const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
-    const int lrel = blockIdx.z, l = a.limb0 + lrel;
+    const int lrel = blockIdx.z + a.lz0, l = a.limb0 + lrel;
     const int o0 = blockIdx.y * TO, c0 = blockIdx.x * TC;
     const u64 q = a.moduli[l];
     const ulonglong2 mu = a.mu[l];
@@ -196,9 +170,8 @@ static cudaError_t launch_src(const WcrtArgs& a, dim3 grid, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st) {
-    if (a.cols % 4 || a.phi % 4 || a.n % 4) return cudaErrorInvalidValue;
-    dim3 grid((a.cols + TC - 1) / TC, (a.phi + TO - 1) / TO, a.limbs);
+static cudaError_t wcrt_cuda_core_launch(const WcrtArgs& a, cudaStream_t st) {
+    dim3 grid((a.cols + TC - 1) / TC, (a.phi + TO - 1) / TO, a.lzn);
     switch (a.source) {
         case kSrcMem:     return launch_src<kSrcMem>(a, grid, st);
         case kSrcI64:     return launch_src<kSrcI64>(a, grid, st);
@@ -208,6 +181,30 @@ cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st) {
         case kSrcGauss:   return launch_src<kSrcGauss>(a, grid, st);
         default: return cudaErrorInvalidValue;
     }
+}
+
+bool wcrt_tc_eligible(const WcrtArgs& a);
+cudaError_t wcrt_tc_launch(const WcrtArgs& a, int nd, cudaStream_t st);
+
+// Limbs are processed in runs that share a digit count: q < 2^48 goes to the tensor-core kernel (4, 5 or 6
+// eight-bit digits), wider moduli (and shapes the tensor-core tiling does not divide) to the CUDA-core kernel.
+// MFHE_WCRT_TC=0 in the environment forces the CUDA-core kernel (A/B measurements and parity tests).
+cudaError_t wcrt_launch(const WcrtArgs& a0, cudaStream_t st) {
+    if (a0.cols % 4 || a0.phi % 4 || a0.n % 4) return cudaErrorInvalidValue;
+    static const bool tc_off = [] { const char* e = std::getenv("MFHE_WCRT_TC"); return e && e[0] == '0'; }();
+    WcrtArgs a = a0;
+    const bool tc = !tc_off && wcrt_tc_eligible(a);
+    auto digits = [&](int lrel) { const int nd = tc ? a.h_ndig[a.limb0 + lrel] : 99; return nd <= 4 ? 4 : nd; };
+    cudaError_t e = cudaSuccess;
+    for (int z = 0; z < a0.limbs && e == cudaSuccess;) {
+        const int nd = digits(z);
+        int z1 = z + 1;
+        while (z1 < a0.limbs && digits(z1) == nd) ++z1;
+        a.lz0 = z; a.lzn = z1 - z;
+        e = (nd <= 6) ? wcrt_tc_launch(a, nd, st) : wcrt_cuda_core_launch(a, st);
+        z = z1;
+    }
+    return e;
 }
 
 }  // namespace mfhe
