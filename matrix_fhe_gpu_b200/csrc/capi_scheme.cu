@@ -37,6 +37,7 @@ WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
     a.n = c->n; a.cols = c->n * c->n; a.limbs = c->L; a.phi = c->phi;
     a.split = c->wsplit; a.delta = c->delta;
     a.tabd = inverse ? c->d_wdig_inv : c->d_wdig_fwd; a.h_ndig = c->ndig.data();
+    a.tabt = inverse ? c->d_wdigt_inv : c->d_wdigt_fwd;
     return a;
 }
 
@@ -44,7 +45,7 @@ WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
 
 extern "C" void mfhe_ctx_destroy(mfhe_ctx* c) {
     if (!c) return;
-    cudaFree(c->d_moduli); cudaFree(c->d_mu); cudaFree(c->d_wtab_fwd); cudaFree(c->d_wtab_inv); cudaFree(c->d_wdig_fwd); cudaFree(c->d_wdig_inv);
+    cudaFree(c->d_moduli); cudaFree(c->d_mu); cudaFree(c->d_wtab_fwd); cudaFree(c->d_wtab_inv); cudaFree(c->d_wdig_fwd); cudaFree(c->d_wdig_inv); cudaFree(c->d_wdigt_fwd); cudaFree(c->d_wdigt_inv);
     cudaFree(c->d_wdft_fwd); cudaFree(c->d_wdft_inv);
     cudaFree(c->d_xyV); cudaFree(c->d_xyVT); cudaFree(c->d_xyVinv); cudaFree(c->d_xyVinvT);
     cudaFree(c->d_crt_Q); cudaFree(c->d_crt_Qhalf); cudaFree(c->d_crt_M); cudaFree(c->d_crt_inv);
@@ -74,6 +75,8 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     std::vector<host::TwPair> mu(L);
     const bool want_digits = (phi % 64 == 0);               // the tensor-core W-CRT tiling (wcrt_tc.cu)
     std::vector<unsigned char> dig_fwd(want_digits ? (size_t)L * 8 * pp : 0), dig_inv(dig_fwd.size());
+    const bool want_tiles = (phi % 128 == 0);                // tcgen05 tiling (wcrt_umma.cu)
+    std::vector<unsigned char> digt_fwd(want_tiles ? (size_t)L * 8 * pp : 0), digt_inv(digt_fwd.size());
     c->ndig.assign(L, 8);
     std::vector<host::cplx> wV, wVinv, xV, xVinv;
     host::CrtTables crt;
@@ -115,6 +118,18 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
                         dig_fwd[((size_t)l * 8 + u) * pp + k] = (unsigned char)(V[k] >> (8 * u));
                         dig_inv[((size_t)l * 8 + u) * pp + k] = (unsigned char)(Vinv[k] >> (8 * u));
                     }
+            if (want_tiles) {
+                const size_t kch = phi / 64;
+                for (size_t o = 0; o < phi; ++o)
+                    for (size_t i = 0; i < phi; ++i) {
+                        const size_t r = o % 128, kk = i % 64;
+                        const size_t idx = ((o / 128) * kch + i / 64) * 8192 + (r / 8) * 512 + (kk / 16) * 128 + (r % 8) * 16 + kk % 16;
+                        for (int u = 0; u < 8; ++u) {
+                            digt_fwd[((size_t)l * 8 + u) * pp + idx] = (unsigned char)(V[o * phi + i] >> (8 * u));
+                            digt_inv[((size_t)l * 8 + u) * pp + idx] = (unsigned char)(Vinv[o * phi + i] >> (8 * u));
+                        }
+                    }
+            }
             const unsigned __int128 m = ~(unsigned __int128)0 / q;
             mu[l] = host::TwPair{(uint64_t)m, (uint64_t)(m >> 64)};
         }
@@ -142,6 +157,7 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     UP(c->d_moduli, c->moduli); UP(c->d_mu, mu); UP(c->d_wtab_fwd, tab_fwd); UP(c->d_wtab_inv, tab_inv);
     UP(c->d_wdft_fwd, wf); UP(c->d_wdft_inv, wi);
     if (want_digits) { UP(c->d_wdig_fwd, dig_fwd); UP(c->d_wdig_inv, dig_inv); }
+    if (want_tiles) { UP(c->d_wdigt_fwd, digt_fwd); UP(c->d_wdigt_inv, digt_inv); }
     UP(c->d_xyV, xV); UP(c->d_xyVT, xVT); UP(c->d_xyVinv, xVinv); UP(c->d_xyVinvT, xVinvT);
     UP(c->d_crt_Q, crt.Q); UP(c->d_crt_Qhalf, crt.Qhalf); UP(c->d_crt_M, crt.M); UP(c->d_crt_inv, crt.inv);
 #undef UP

@@ -24,6 +24,8 @@ struct mfhe_ctx {
     int wsplit = 0;                           // 1: tables stored as {lo26, hi} pairs (all q < 2^52)
     unsigned char* d_wdig_fwd = nullptr;      // [L][8 digits][o][i] bytes: the same tables cut into 8-bit digits,
     unsigned char* d_wdig_inv = nullptr;      //   K-major, for the tensor-core W-CRT (wcrt_tc.cu)
+    unsigned char* d_wdigt_fwd = nullptr;     // the same digits pre-tiled into UMMA core-matrix blocks
+    unsigned char* d_wdigt_inv = nullptr;     //   [L][8][o/128][i/64][8 KiB] for the tcgen05 W-CRT (wcrt_umma.cu)
     std::vector<int> ndig;                    // [L] ceil(bits(q_l) / 8)
     double2* d_wdft_fwd = nullptr;            // [i = r][o = w]
     double2* d_wdft_inv = nullptr;            // [i = w][o = r]
@@ -64,6 +66,7 @@ struct WcrtArgs {
     int split = 0;
     double delta = 0;
     const unsigned char* tabd = nullptr;   // digit tables [limbs][8][phi][phi] (tensor-core path), may be null
+    const unsigned char* tabt = nullptr;   // digit tables pre-tiled for UMMA (tcgen05 path), may be null
     const int* h_ndig = nullptr;           // HOST array [limbs]: 8-bit digits per modulus
     int lz0 = 0, lzn = 0;                  // relative limb window of one launch (set by wcrt_launch)
 };

@@ -185,23 +185,31 @@ static cudaError_t wcrt_cuda_core_launch(const WcrtArgs& a, cudaStream_t st) {
 
 bool wcrt_tc_eligible(const WcrtArgs& a);
 cudaError_t wcrt_tc_launch(const WcrtArgs& a, int nd, cudaStream_t st);
+bool wcrt_umma_eligible(const WcrtArgs& a);
+cudaError_t wcrt_umma_launch(const WcrtArgs& a, int nd, cudaStream_t st);
 
-// Limbs are processed in runs that share a digit count: q < 2^48 goes to the tensor-core kernel (4, 5 or 6
-// eight-bit digits), wider moduli (and shapes the tensor-core tiling does not divide) to the CUDA-core kernel.
-// MFHE_WCRT_TC=0 in the environment forces the CUDA-core kernel (A/B measurements and parity tests).
+// Limbs are processed in runs that share a digit count.  q < 2^48 goes to the tensor cores (4, 5 or 6 eight-bit
+// digits): the tcgen05 / TMEM kernel (wcrt_umma.cu) when the shape divides its 128 x 32 x 64 tiling, else the
+// mma.sync kernel (wcrt_tc.cu); wider moduli and other shapes go to the CUDA-core kernel above.
+// MFHE_WCRT_PATH = umma | mma | cuda in the environment pins the choice (A/B measurements, parity tests).
 cudaError_t wcrt_launch(const WcrtArgs& a0, cudaStream_t st) {
     if (a0.cols % 4 || a0.phi % 4 || a0.n % 4) return cudaErrorInvalidValue;
-    static const bool tc_off = [] { const char* e = std::getenv("MFHE_WCRT_TC"); return e && e[0] == '0'; }();
+    const int pin = [] {
+        const char* e = std::getenv("MFHE_WCRT_PATH");
+        if (!e) return 0;
+        return e[0] == 'u' ? 1 : e[0] == 'm' ? 2 : e[0] == 'c' ? 3 : 0;
+    }();
     WcrtArgs a = a0;
-    const bool tc = !tc_off && wcrt_tc_eligible(a);
-    auto digits = [&](int lrel) { const int nd = tc ? a.h_ndig[a.limb0 + lrel] : 99; return nd <= 4 ? 4 : nd; };
+    const bool umma = (pin == 0 || pin == 1) && wcrt_umma_eligible(a);
+    const bool mma = !umma && pin != 3 && wcrt_tc_eligible(a);
+    auto digits = [&](int lrel) { const int nd = (umma || mma) ? a.h_ndig[a.limb0 + lrel] : 99; return nd <= 4 ? 4 : nd; };
     cudaError_t e = cudaSuccess;
     for (int z = 0; z < a0.limbs && e == cudaSuccess;) {
         const int nd = digits(z);
         int z1 = z + 1;
         while (z1 < a0.limbs && digits(z1) == nd) ++z1;
         a.lz0 = z; a.lzn = z1 - z;
-        e = (nd <= 6) ? wcrt_tc_launch(a, nd, st) : wcrt_cuda_core_launch(a, st);
+        e = (nd > 6) ? wcrt_cuda_core_launch(a, st) : umma ? wcrt_umma_launch(a, nd, st) : wcrt_tc_launch(a, nd, st);
         z = z1;
     }
     return e;

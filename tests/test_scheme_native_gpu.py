@@ -105,3 +105,32 @@ def test_native_encrypt_bit_exact_vs_oracle(G, Or, cuda_device):
     ocr, oci = Or.encrypt_pair_with(m_re, m_im, host(sk), a, e, e)
     assert (host(cr) == ocr).all() and (host(ci) == oci).all()
     assert (host(g.decrypt_to_eval(cr, sk, S.POLY)) == Or.decrypt_to_eval(ocr, host(sk))).all()
+
+
+def test_native_wcrt_three_paths_identical(G, cuda_device, monkeypatch):
+    """The tcgen05 (TMEM) kernel, the mma.sync kernel and the CUDA-core kernel give the same words for every
+    layout pair and every fused source; the CUDA-core kernel is the one checked against the oracle on the
+    small shapes of test_scheme_gpu.py, the default (tcgen05) one by the tests above."""
+    import torch
+    S, g = G
+    a = g.sample_uniform()
+    m = dev(msg("e2e"), cuda_device)
+    i64 = torch.arange(g.phi * g.n2, dtype=torch.int64, device=cuda_device).reshape(g.phi, g.n2) % 17 - 8
+    ref = None
+    for path in ("cuda", "mma", "umma"):
+        monkeypatch.setenv("MFHE_WCRT_PATH", path)
+        got = []
+        for lin, lout in ((S.MATRIX, S.POLY), (S.POLY, S.MATRIX), (S.MATRIX, S.MATRIX)):
+            got.append(g.wntt_forward_matrix(a, lin, lout).clone())
+            got.append(g.wntt_inverse_matrix(a, lin, lout).clone())
+        re, im = g.encode_to_wntt_eval(m)                 # quantiser sources
+        got += [re.clone(), im.clone()]
+        got.append(g.wntt_forward_centered(i64.reshape(-1)).clone())      # int64 source + CRT compose
+        got.append(g.sample_gaussian().clone())
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = got
+        else:
+            for k, (x, y) in enumerate(zip(ref, got)):
+                assert torch.equal(x, y), f"path {path} differs from cuda-core at output {k}"
+    monkeypatch.delenv("MFHE_WCRT_PATH")
