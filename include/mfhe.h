@@ -140,7 +140,8 @@ const mfhe_ntt_plan *mfhe_ctx_xy_plan(const mfhe_ctx *ctx);
 int mfhe_ctx_copy_xy_matrix(const mfhe_ctx *ctx, int which, double *d_out, void *stream);
 
 /* ---- W-CRT: wntt_forward_matrix / wntt_inverse_matrix (HE.cu:437-452, 716-781) with explicit
- * layouts (reference: forward MATRIX -> POLY, inverse POLY -> MATRIX); out must not alias in. */
+ * layouts (reference: forward MATRIX -> POLY, inverse POLY -> MATRIX); out must not alias in.
+ * Inputs are canonical residues (< q of their limb), as every producer on the path emits them. */
 int mfhe_wcrt_forward(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, int in_layout, int out_layout, void *stream);
 int mfhe_wcrt_inverse(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, int in_layout, int out_layout, void *stream);
 /* wntt_forward_vector_kernel (HE.cu:1245-1270): [w][limb][x] */

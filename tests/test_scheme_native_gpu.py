@@ -120,9 +120,11 @@ def test_native_wcrt_three_paths_identical(G, cuda_device, monkeypatch):
     for path in ("cuda", "mma", "umma"):
         monkeypatch.setenv("MFHE_WCRT_PATH", path)
         got = []
-        for lin, lout in ((S.MATRIX, S.POLY), (S.POLY, S.MATRIX), (S.MATRIX, S.MATRIX)):
-            got.append(g.wntt_forward_matrix(a, lin, lout).clone())
-            got.append(g.wntt_inverse_matrix(a, lin, lout).clone())
+        a_poly = g.layout_convert(a, S.MATRIX, S.POLY)          # inputs must be canonical residues of THEIR limb
+        for lin, lout in ((S.MATRIX, S.POLY), (S.POLY, S.MATRIX), (S.MATRIX, S.MATRIX), (S.POLY, S.POLY)):
+            x = a_poly if lin == S.POLY else a
+            got.append(g.wntt_forward_matrix(x, lin, lout).clone())
+            got.append(g.wntt_inverse_matrix(x, lin, lout).clone())
         re, im = g.encode_to_wntt_eval(m)                 # quantiser sources
         got += [re.clone(), im.clone()]
         got.append(g.wntt_forward_centered(i64.reshape(-1)).clone())      # int64 source + CRT compose
