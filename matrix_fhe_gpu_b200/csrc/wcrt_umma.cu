@@ -10,23 +10,33 @@
 // adds a_u b_v into position u+v for every v at once: ND instructions of shape 128 x (32 ND) x 32 per K step
 // instead of ND^2 small ones, and every A tile is read from shared memory once per K step.
 //
-//   CTA tile   128 outputs o  x  32 columns c, all K (phi) in chunks of 64, NS-stage ring in shared memory
-//   warp 0     lane 0 streams the table digits: the table is stored pre-tiled in the UMMA canonical
-//              (no-swizzle, K-major, 8x16-byte core matrices) layout, so one 8 KiB cp.async.bulk per digit plane
-//              and chunk lands a ready-to-use A tile; completion through an mbarrier (complete_tx)
-//   warps 4-7  produce B': fused source (memory in either layout / int64 / quantiser / samplers) -> canonical
-//              u64 residues, four consecutive i per thread -> PRMT byte transpose -> K-major core matrices,
-//              fence.proxy.async, mbarrier arrive
-//   warp 1     lane 0 issues the tcgen05.mma's and commits them to the stage's "empty" barrier
-//   all warps  epilogue: tcgen05.ld the 2ND-1 partial sums of 8 columns, recombine to 128 bits, ONE Barrett
-//              reduction per output, 16-byte stores in either layout.
+//   PERSISTENT CTAs (one per SM, 17 warps) walk over the 128 (o) x 32 (c) tiles; K (phi) in chunks of 64 through an
+//   NS-stage ring in shared memory that runs on across tile boundaries, so the next tile's operands are
+//   already landing while the current tile is in its epilogue.
+//   warp 16    one thread issues the tcgen05.mma's (commit -> the stage's "empty" barrier, last chunk -> "tmem
+//              full") and, while they run, refills the stage released by the previous chunk with table digits:
+//              the table is stored pre-tiled in the UMMA canonical (no-swizzle, K-major, 8 x 16-byte core
+//              matrices) layout, so one 8 KiB cp.async.bulk per digit plane and chunk lands a ready-to-use A
+//              tile; completion through an mbarrier (complete_tx).
+//   warps 0-7  produce B' (two groups of 4 warps on alternate chunks): fused source (memory in either layout /
+//              int64 / quantiser / samplers) -> canonical u64 residues, LDG.128 of two columns x four
+//              consecutive i per item -> PRMT byte transposes -> K-major core matrices, fence.proxy.async,
+//              mbarrier arrive.
+//   warps 8-15 epilogue: wait for the tile's last commit, tcgen05.ld the 2ND-1 partial sums of 8 columns,
+//              recombine to 128 bits, ONE Barrett reduction per output, 16-byte stores in either layout; TMEM is
+//              handed back to the issuer as soon as the last accumulator column is in registers.  No zero-fill:
+//              the first K step of a tile is issued as overwrite / accumulate pieces.
 #include "ctx.h"
 #include "wcrt_common.cuh"
+
+#ifndef MFHE_UMMA_DBG
+#define MFHE_UMMA_DBG 0      // timing experiments only: 1 = no table copies, 2 = no input loads, 4 = no epilogue arithmetic
+#endif
 
 namespace mfhe {
 
 namespace {
-constexpr int UM = 128, UN = 32, UKC = 64, UTHREADS = 256;
+constexpr int UM = 128, UN = 32, UKC = 64, UTHREADS = 544;
 constexpr int A_PLANE = UM * UKC;            // 8 KiB: one digit plane of one A chunk
 constexpr int B_PLANE = UN * UKC;            // 2 KiB
 
@@ -56,10 +66,10 @@ __device__ __forceinline__ void bulk_g2s(u32 dst, const void* src, u32 bytes, u3
 __device__ __forceinline__ u64 umma_desc(u32 saddr, u32 lbo, u32 sbo) {
     return (u64)((saddr & 0x3FFFFu) >> 4) | ((u64)(lbo >> 4) << 16) | ((u64)(sbo >> 4) << 32) | (1ull << 46);
 }
-__device__ __forceinline__ void umma_i8(u32 d_tmem, u64 adesc, u64 bdesc, u32 idesc) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 0;\n\t"
+__device__ __forceinline__ void umma_i8(u32 d_tmem, u64 adesc, u64 bdesc, u32 idesc, u32 accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                  "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc) : "memory");
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(u32 bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -68,6 +78,10 @@ __device__ __forceinline__ void tmem_ld8(u32 taddr, u32 (&r)[8]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld4(u32 taddr, u32 (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
 }
 __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
     const u32 z = 0;
@@ -78,38 +92,41 @@ __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
 template <int ND> struct UmmaCfg {
     static constexpr int NS = (ND <= 5) ? 4 : 3;                       // ring stages
     static constexpr int STAGE = ND * (A_PLANE + B_PLANE);
-    static constexpr int SMEM = NS * STAGE + 1024;                      // + barriers / TMEM pointer, 1 KiB align slack
-    static constexpr int NPRIME = ND * UN;                              // N of one instruction
+    static constexpr int SMEM = NS * STAGE + 1024;                      // + barriers / TMEM pointer, alignment slack
     static constexpr int ACC_COLS = (2 * ND - 1) * UN;
-    // kind::i8 instruction descriptor: D = s32, A = B = unsigned 8 bit, both K-major, N' x 128
-    static constexpr u32 IDESC = (2u << 4) | ((u32)(NPRIME >> 3) << 17) | ((u32)(UM >> 4) << 24);
+    // kind::i8 instruction descriptor: D = s32, A = B = unsigned 8 bit, both K-major, 128 x N
+    __host__ __device__ static constexpr u32 idesc(int n) { return (2u << 4) | ((u32)(n >> 3) << 17) | ((u32)(UM >> 4) << 24); }
 };
+
+// tile id -> (relative limb, column block, output block); the output block runs fastest so that the CTAs
+// working at the same time share the table panels in L2 and read every input column block once from HBM
+struct TileIdx { int lz, cblk, ot; };
+__device__ __forceinline__ TileIdx tile_decode(int tile, int nOT, int nCB) {
+    TileIdx r; r.ot = tile % nOT; const int x = tile / nOT; r.cblk = x % nCB; r.lz = x / nCB; return r;
+}
 
 template <int SRC, int ND>
 __global__ void __launch_bounds__(UTHREADS, 1)
-wcrt_umma_kernel(const WcrtArgs a) {
+wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     using C = UmmaCfg<ND>;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
-    unsigned char* ctrl = smem + C::NS * C::STAGE;                     // barriers: fullA[NS], fullB[NS], empty[NS], acc
+    unsigned char* ctrl = smem + C::NS * C::STAGE;        // barriers: fullA[NS], fullB[NS], empty[NS], tmem_full, tmem_empty
     const u32 bar0 = smem_u32(ctrl);
     auto bar_fullA = [&](int s) { return bar0 + 8u * s; };
     auto bar_fullB = [&](int s) { return bar0 + 8u * (C::NS + s); };
     auto bar_empty = [&](int s) { return bar0 + 8u * (2 * C::NS + s); };
-    const u32 bar_acc = bar0 + 8u * (3 * C::NS);
-    volatile u32* tmem_slot = reinterpret_cast<volatile u32*>(ctrl + 8 * (3 * C::NS + 1));
+    const u32 bar_tfull = bar0 + 8u * (3 * C::NS), bar_tempty = bar0 + 8u * (3 * C::NS + 1);
+    volatile u32* tmem_slot = reinterpret_cast<volatile u32*>(ctrl + 8 * (3 * C::NS + 2));
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int lrel = blockIdx.z + a.lz0, l = a.limb0 + lrel;
-    const int ot = blockIdx.y, o0 = ot * UM, c0 = blockIdx.x * UN;
-    const u64 q = a.moduli[l];
-    const ulonglong2 mu = a.mu[l];
-    const int kchunks = a.phi / UKC;
-    const int lsrc = (SRC == kSrcMem) ? lrel : l;
+    const int kchunks = a.phi / UKC, nOT = a.phi / UM, nCB = a.cols / UN;
+    const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int my_chunks = my_tiles * kchunks;
 
     if (t == 0) {
         for (int s = 0; s < C::NS; ++s) { mbar_init(bar_fullA(s), 1); mbar_init(bar_fullB(s), 128); mbar_init(bar_empty(s), 1); }
-        mbar_init(bar_acc, 1);
+        mbar_init(bar_tfull, 1); mbar_init(bar_tempty, 8);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -121,41 +138,29 @@ wcrt_umma_kernel(const WcrtArgs a) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const u32 tmem = *tmem_slot;
-    const u32 tlane = tmem + ((u32)(32 * (warp & 3)) << 16);
 
-    // zero the accumulator columns (every instruction accumulates)
-    {
-        constexpr int G = C::ACC_COLS / 8, H = (G + 1) / 2;
-        const int g0 = (warp >> 2) * H, g1 = (g0 + H < G) ? g0 + H : G;
-        for (int gi = g0; gi < g1; ++gi) tmem_st8_zero(tlane + 8u * gi);
-        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-
-    if (warp == 0) {
-        // ===== table-digit producer: one bulk copy per digit plane and chunk =====
+    if (warp == 16) {
+        // ===== one thread: issues the MMAs and streams the table digits (one bulk copy per digit plane and chunk) =====
         if (lane == 0) {
-            const unsigned char* base = a.tabt + (size_t)l * 8 * a.phi * a.phi;
-            for (int kt = 0; kt < kchunks; ++kt) {
-                const int s = kt % C::NS;
-                if (kt >= C::NS) mbar_wait(bar_empty(s), ((kt / C::NS) - 1) & 1);
+            auto issue_A = [&](int g) {
+                const int s = g % C::NS, kt = g % kchunks;
+                const TileIdx ti = tile_decode((int)blockIdx.x + (g / kchunks) * (int)gridDim.x, nOT, nCB);
+                const unsigned char* base = a.tabt + (size_t)(a.limb0 + a.lz0 + ti.lz) * 8 * a.phi * a.phi;
+#if MFHE_UMMA_DBG & 1
+                mbar_arrive(bar_fullA(s)); return;
+#endif
                 mbar_expect_tx(bar_fullA(s), ND * A_PLANE);
                 const u32 dst = smem_u32(smem + s * C::STAGE);
 #pragma unroll
                 for (int u = 0; u < ND; ++u)
                     bulk_g2s(dst + u * A_PLANE,
-                             base + ((size_t)u * a.phi * a.phi) + ((size_t)ot * kchunks + kt) * A_PLANE, A_PLANE, bar_fullA(s));
-            }
-        }
-        __syncwarp();
-    } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int kt = 0; kt < kchunks; ++kt) {
-                const int s = kt % C::NS;
-                const u32 par = (kt / C::NS) & 1;
+                             base + ((size_t)u * a.phi * a.phi) + ((size_t)ti.ot * kchunks + kt) * A_PLANE, A_PLANE, bar_fullA(s));
+            };
+            for (int g = 0; g < C::NS && g < my_chunks; ++g) issue_A(g);
+            for (int g = 0; g < my_chunks; ++g) {
+                const int s = g % C::NS, kt = g % kchunks, it = g / kchunks;
+                const u32 par = (g / C::NS) & 1;
+                if (kt == 0 && it > 0) mbar_wait(bar_tempty, (it - 1) & 1);      // epilogue has drained the accumulators
                 mbar_wait(bar_fullA(s), par);
                 mbar_wait(bar_fullB(s), par);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -163,85 +168,183 @@ wcrt_umma_kernel(const WcrtArgs a) {
 #pragma unroll
                 for (int ks = 0; ks < UKC / 32; ++ks) {
                     const u64 bdesc = umma_desc(sb + ks * 256, 128, 512);
+                    if (kt == 0 && ks == 0) {
+                        // first K step of a tile: nothing to accumulate onto.  Position block u+ND-1 is new for
+                        // every u, the others were started by u-1: split the instruction accordingly.
+                        umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, C::idesc(ND * UN), 0);
 #pragma unroll
-                    for (int u = 0; u < ND; ++u)
-                        umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE + ks * 256, 128, 512), bdesc, C::IDESC);
+                        for (int u = 1; u < ND; ++u) {
+                            const u64 adesc = umma_desc(sa + u * A_PLANE, 128, 512);
+                            umma_i8(tmem + (u32)(u * UN), adesc, bdesc, C::idesc((ND - 1) * UN), 1);
+                            umma_i8(tmem + (u32)((u + ND - 1) * UN), adesc, umma_desc(sb + (ND - 1) * B_PLANE, 128, 512),
+                                    C::idesc(UN), 0);
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < ND; ++u)
+                            umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE + ks * 256, 128, 512), bdesc,
+                                    C::idesc(ND * UN), 1);
+                    }
                 }
                 umma_commit(bar_empty(s));
+                if (kt == kchunks - 1) umma_commit(bar_tfull);
+                // while chunk g runs, refill the stage chunk g-1 has just released
+                if (g >= 1 && g - 1 + C::NS < my_chunks) {
+                    mbar_wait(bar_empty((g - 1) % C::NS), ((g - 1) / C::NS) & 1);
+                    issue_A(g - 1 + C::NS);
+                }
             }
-            umma_commit(bar_acc);
         }
         __syncwarp();
-    } else if (warp >= 4) {
-        // ===== input-digit producers (128 threads): item = (column c, four consecutive i) =====
-        const int pt = t - 128;
-        for (int kt = 0; kt < kchunks; ++kt) {
-            const int s = kt % C::NS;
-            if (kt >= C::NS) mbar_wait(bar_empty(s), ((kt / C::NS) - 1) & 1);
+    } else if (warp < 8) {
+        // ===== input-digit producers: two groups of 128 threads take alternate chunks.  Item = (column pair, four
+        // consecutive i): 4 LDG.128, two PRMT byte transposes, K-major core-matrix stores.  The loads of a group's
+        // next chunk (two chunks = one MMA chunk time ahead) are in flight while the current one is converted. =====
+        const int grp = warp >> 2, pt = t & 127;
+        int ic[2], ikq[2], isw[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const int id = pt + 128 * r;                           // 256 items per chunk
+            isw[r] = (id >> 4) & 1;
+            ic[r] = ((id >> 5) & 3) * 8 + (id & 3) * 2;
+            ikq[r] = ((id >> 2) & 3) | (isw[r] << 2) | (((id >> 7) & 1) << 3);
+        }
+        const size_t istride = (size_t)a.limbs * a.cols;
+        // fetch-side cursor over this group's chunks
+        int f_kt = grp, f_it = 0;
+        size_t f_off[2] = {0, 0};
+        int f_lrel = 0, f_l = 0, f_c0 = 0;
+        u64 f_q = 0, f_mu = 0;
+        auto f_tile = [&]() {
+            const TileIdx ti = tile_decode((int)blockIdx.x + f_it * (int)gridDim.x, nOT, nCB);
+            f_lrel = a.lz0 + ti.lz; f_l = a.limb0 + f_lrel; f_c0 = ti.cblk * UN;
+            if constexpr (SRC == kSrcMem) {
+#pragma unroll
+                for (int r = 0; r < 2; ++r) f_off[r] = poly_set_addr(a.in_layout, 0, f_lrel, f_c0 + ic[r], a.n, a.cols, a.limbs);
+            } else { f_q = a.moduli[f_l]; f_mu = a.mu[f_l].y; }
+        };
+        auto fetch = [&](u64 (&rb)[2][8]) {
+            if (f_kt == grp) f_tile();
+#pragma unroll
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int i = f_kt * UKC + 4 * ikq[r] + j;
+#if MFHE_UMMA_DBG & 2
+                    rb[r][2 * j] = (u64)(i + f_lrel); rb[r][2 * j + 1] = (u64)i;
+#else
+                    if constexpr (SRC == kSrcMem) {
+                        const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>((const u64*)a.in + (size_t)i * istride + f_off[r]));
+                        rb[r][2 * j] = v.x; rb[r][2 * j + 1] = v.y;
+                    } else {
+                        rb[r][2 * j] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r], f_q, f_mu);
+                        rb[r][2 * j + 1] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r] + 1, f_q, f_mu);
+                    }
+#endif
+                }
+            f_kt += 2;
+            if (f_kt >= kchunks) { f_kt = grp; ++f_it; }
+        };
+        auto stash = [&](int g, const u64 (&rb)[2][8]) {
+            const int s = g % C::NS;
+            if (g >= C::NS) mbar_wait(bar_empty(s), ((g / C::NS) - 1) & 1);
             unsigned char* sB = smem + s * C::STAGE + ND * A_PLANE;
-            u64 rb[4][4];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int id = pt + 128 * r;                       // 512 items: c = id & 31 (low 3 bits + bits 5,6), kq
-                const int c = ((id >> 5) & 3) * 8 + (id & 7), kq = ((id >> 7) & 3) * 4 + ((id >> 3) & 3);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) rb[r][j] = wcrt_load_one<SRC>(a, kt * UKC + 4 * kq + j, lsrc, c0 + c, q, mu.y);
-            }
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int id = pt + 128 * r;
-                const int c = ((id >> 5) & 3) * 8 + (id & 7), kq = ((id >> 7) & 3) * 4 + ((id >> 3) & 3);
-                // row (v*32 + c) of B', bytes [4kq, 4kq+4): core matrix (row/8, kq/4), row%8, (kq%4)*4
-                unsigned char* dst = sB + (c >> 3) * 512 + (kq >> 2) * 128 + (c & 7) * 16 + (kq & 3) * 4;
-                const u32 l0 = (u32)rb[r][0], l1 = (u32)rb[r][1], l2 = (u32)rb[r][2], l3 = (u32)rb[r][3];
-                const u32 h0 = (u32)(rb[r][0] >> 32), h1 = (u32)(rb[r][1] >> 32), h2 = (u32)(rb[r][2] >> 32), h3 = (u32)(rb[r][3] >> 32);
+            for (int r = 0; r < 2; ++r) {
+                // rows (v*32 + c), (v*32 + c + 1) of B', bytes [4kq, 4kq+4): core matrix (row/8, kq/4), row%8, (kq%4)*4.
+                // Lanes with isw set store the odd row first, so that one store instruction covers all 32 banks.
+                unsigned char* dst = sB + (ic[r] >> 3) * 512 + (ikq[r] >> 2) * 128 + (ic[r] & 7) * 16 + (ikq[r] & 3) * 4;
+                unsigned char* d1 = dst + (isw[r] ? 16 : 0);
+                unsigned char* d2 = dst + (isw[r] ? 0 : 16);
 #pragma unroll
                 for (int v = 0; v < ND; ++v) {
-                    const u32 x0 = v < 4 ? l0 : h0, x1 = v < 4 ? l1 : h1, x2 = v < 4 ? l2 : h2, x3 = v < 4 ? l3 : h3;
+                    const int sh = (v < 4) ? 0 : 32;
                     const u32 sel = (u32)(v & 3) | ((u32)(4 + (v & 3)) << 4);
-                    const u32 t01 = __byte_perm(x0, x1, sel), t23 = __byte_perm(x2, x3, sel);
-                    *reinterpret_cast<u32*>(dst + v * B_PLANE) = __byte_perm(t01, t23, 0x5410);
+                    u32 wd[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const u32 x0 = (u32)(rb[r][0 + e] >> sh), x1 = (u32)(rb[r][2 + e] >> sh);
+                        const u32 x2 = (u32)(rb[r][4 + e] >> sh), x3 = (u32)(rb[r][6 + e] >> sh);
+                        wd[e] = __byte_perm(__byte_perm(x0, x1, sel), __byte_perm(x2, x3, sel), 0x5410);
+                    }
+                    *reinterpret_cast<u32*>(d1 + v * B_PLANE) = isw[r] ? wd[1] : wd[0];
+                    *reinterpret_cast<u32*>(d2 + v * B_PLANE) = isw[r] ? wd[0] : wd[1];
                 }
             }
+#if !(MFHE_UMMA_DBG & 8)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
             mbar_arrive(bar_fullB(s));
+        };
+        u64 rb0[2][8], rb1[2][8];
+        if (grp < my_chunks) fetch(rb0);
+        for (int g = grp; g < my_chunks; g += 4) {              // kchunks is even, so is my_chunks
+            const bool more = g + 2 < my_chunks;
+            if (more) fetch(rb1);
+            stash(g, rb0);
+            if (more) {
+                if (g + 4 < my_chunks) fetch(rb0);
+                stash(g + 2, rb1);
+            }
         }
-    }
-
-    // ===== epilogue (all warps): lanes 32*(warp%4) .. +31 = rows, column half warp/4 =====
-    mbar_wait(bar_acc, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const int o = o0 + 32 * (warp & 3) + lane;
-#pragma unroll 1
-    for (int cg = 0; cg < 2; ++cg) {
-        const int cc = (warp >> 2) * 16 + cg * 8;
-        u32 acc[2 * ND - 1][8];
+    } else if (warp >= 8) {
+        // ===== epilogue (8 warps): TMEM lanes 32*(warp%4).. = output rows, column half (warp-8)/4 =====
+        const u32 tlane = tmem + ((u32)(32 * (warp & 3)) << 16);
+        for (int it = 0; it < my_tiles; ++it) {
+            const TileIdx ti = tile_decode((int)blockIdx.x + it * (int)gridDim.x, nOT, nCB);
+            const int lrel = a.lz0 + ti.lz, l = a.limb0 + lrel;
+            const u64 q = a.moduli[l];
+            const ulonglong2 mu = a.mu[l];
+            const int o = ti.ot * UM + 32 * (warp & 3) + lane;
+            mbar_wait(bar_tfull, it & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // phase 1 (holds TMEM): fold the 2ND-1 partial sums of each of this thread's 16 outputs into
+            //   lo = sum_{w<5} S_w 2^(8w)  (< 2^61)   and   up = sum_{5<=w<10} S_w 2^(8(w-5))  (< 2^61)   [+ S_10 for ND = 6],
+            // 4 columns at a time to keep the register footprint small
+            const int ccol = ((warp - 8) >> 2) * 16;
+            u64 vlo[16], vup[16];
+            u32 vtop[(2 * ND - 1 > 10) ? 16 : 1];         // position 10 (scale 2^80) exists for ND = 6 only
 #pragma unroll
-        for (int w = 0; w < 2 * ND - 1; ++w) tmem_ld8(tlane + (u32)(w * UN + cc), acc[w]);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        u64 r[8];
+            for (int sg = 0; sg < 4; ++sg) {
+                u32 acc[2 * ND - 1][4];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            u64 lo = 0, hi = 0;
+                for (int w = 0; w < 2 * ND - 1; ++w) tmem_ld4(tlane + (u32)(w * UN + ccol + 4 * sg), acc[w]);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-            for (int w = 0; w < 2 * ND - 1; ++w) {
-                const u64 sv = (u64)acc[w][e];
-                const int sh = 8 * w;
-                if (sh < 64) {
-                    const u64 x = sv << sh;
-                    lo += x; hi += (lo < x);
-                    if (sh > 32) hi += sv >> (64 - sh);
-                } else {
-                    hi += sv << (sh - 64);
+                for (int e = 0; e < 4; ++e) {
+                    u64 lo = acc[0][e], up = acc[5 < 2 * ND - 1 ? 5 : 0][e];
+#pragma unroll
+                    for (int w = 1; w < 5 && w < 2 * ND - 1; ++w) lo += (u64)acc[w][e] << (8 * w);
+#pragma unroll
+                    for (int w = 6; w < 2 * ND - 1 && w < 10; ++w) up += (u64)acc[w][e] << (8 * (w - 5));
+                    if (2 * ND - 1 <= 5) up = 0;
+                    vlo[4 * sg + e] = lo; vup[4 * sg + e] = up;
+                    if constexpr (2 * ND - 1 > 10) vtop[4 * sg + e] = acc[10][e];
                 }
             }
-            r[e] = reduce128(lo, hi, q, mu.x, mu.y);
-        }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty);                 // the issuer may start the next tile
+#if MFHE_UMMA_DBG & 4
+            if (vlo[0] == 0x12345678u) a.out[0] = vup[1];
+            continue;
+#endif
+            // phase 2 (overlaps the next tile's MMAs): value = lo + up * 2^40, one Barrett reduction, 16-byte stores
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-            const size_t off = poly_set_addr(a.out_layout, o, lrel, c0 + cc + e, a.n, a.cols, a.limbs);
-            *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[e], r[e + 1]);
-            if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[e], r[e + 1]);
+            for (int e = 0; e < 16; e += 2) {
+                u64 r[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const u64 x = vup[e + k] << 40;
+                    const u64 lo = vlo[e + k] + x;
+                    u64 hi = (vup[e + k] >> 24) + (lo < x);
+                    if constexpr (2 * ND - 1 > 10) hi += (u64)vtop[e + k] << 16;
+                    r[k] = reduce128(lo, hi, q, mu.x, mu.y);
+                }
+                const size_t off = poly_set_addr(a.out_layout, o, lrel, ti.cblk * UN + ccol + e, a.n, a.cols, a.limbs);
+                *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[0], r[1]);
+                if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[0], r[1]);
+            }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -260,8 +363,10 @@ static cudaError_t launch_umma_nd(const WcrtArgs& a, cudaStream_t st) {
         if (e != cudaSuccess) return e;
         attr = true;
     }
-    dim3 grid(a.cols / UN, a.phi / UM, a.lzn);
-    wcrt_umma_kernel<SRC, ND><<<grid, UTHREADS, C::SMEM, st>>>(a);
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    const int ntiles = (a.cols / UN) * (a.phi / UM) * a.lzn;
+    wcrt_umma_kernel<SRC, ND><<<ntiles < sms ? ntiles : sms, UTHREADS, C::SMEM, st>>>(a, ntiles);
     return cudaGetLastError();
 }
 
@@ -276,7 +381,7 @@ static cudaError_t launch_umma_src(const WcrtArgs& a, int nd, cudaStream_t st) {
 }
 
 bool wcrt_umma_eligible(const WcrtArgs& a) {
-    return a.tabt && a.h_ndig && a.phi % UM == 0 && a.phi % UKC == 0 && a.cols % UN == 0 && a.n % 2 == 0;
+    return a.tabt && a.h_ndig && a.phi % UM == 0 && a.phi % (2 * UKC) == 0 && a.cols % UN == 0 && a.n % 2 == 0;
 }
 
 cudaError_t wcrt_umma_launch(const WcrtArgs& a, int nd, cudaStream_t st) {
