@@ -34,6 +34,13 @@ LOGN, LIMBS, BATCH, BITS = 16, 32, 64, 60
 N = 1 << LOGN
 LIMB_POLYS = LIMBS * BATCH
 ALGO_BYTES_PER_TRANSFORM = 16 * N                # 8 B read + 8 B write per coefficient
+# dram__bytes_read.sum + dram__bytes_write.sum of the two launches of one INVERSE transform (rows + columns kernel)
+# of this workload, from the committed `ncu --set full` capture profiles/r1_07_ncu_ntt_summary.txt
+NCU_DRAM_BYTES_INVERSE = int((1.482865 + 1.026216 + 1.073982 + 1.014492) * 1e9)
+NCU_DRAM_BYTES_FORWARD = int((1.074171 + 1.026351 + 1.440122 + 1.026373) * 1e9)
+# register-only butterfly rate of the same arithmetic on this GPU (profiles/r1_04_intpipe.log, "CT bfly approx-quotient"):
+# the integer (fmaheavy) pipe, not HBM, binds these kernels -- reported next to the HBM fraction
+INT_PIPE_BFLY_PER_S_PER_SM = 7.02e9
 
 
 def peaks():
@@ -322,7 +329,17 @@ def main():
                     "path": "mfhe_ntt_forward_host + mfhe_ntt_inverse_host on pinned host memory"},
             "gpu_launches": 4 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak,
+                         "traffic": NCU_DRAM_BYTES_INVERSE if t_inv >= t_fwd else NCU_DRAM_BYTES_FORWARD,
+                         "traffic_note": "two launches (row + column kernel) = two passes over the data; ncu capture "
+                                         "profiles/r1_07_ncu_ntt_summary.txt",
+                         "algorithmic_bytes_per_launch_pair": algo,
+                         "int_pipe": {"butterflies_per_s": LIMB_POLYS * (N // 2) * LOGN / worst,
+                                      "peak_butterflies_per_s": INT_PIPE_BFLY_PER_S_PER_SM * 148,
+                                      "frac": LIMB_POLYS * (N // 2) * LOGN / worst / (INT_PIPE_BFLY_PER_S_PER_SM * 148),
+                                      "note": "binding roofline: fmaheavy pipe 74-80 % busy in ncu; peak = register-only "
+                                              "butterfly loop measured on this B200 (profiles/r1_04_intpipe.log)"},
+                         "peak_source": peak_src,
                          "kernel": "slower of forward (ntt_cols_kernel+ntt_rows_fwd_kernel) and inverse "
                                    "(ntt_rows_inv_kernel+ntt_cols_kernel) transform; algorithmic bytes = "
                                    "16*N per limb-poly per transform",
