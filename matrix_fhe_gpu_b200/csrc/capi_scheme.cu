@@ -431,7 +431,13 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
     if (e == cudaSuccess) {
         WcrtArgs g = wcrt_args(c, false);
         g.source = e_src; g.in = e_re; g.out = E0;
-        e = wcrt_launch(g, st);
+        if (e_src == kSrcGauss) {
+            signed char* tab = (signed char*)c->take((size_t)c->phi * c->n2());
+            if (!tab) return fail(MFHE_ENOMEM, std::string(who) + ": arena too small");
+            e = gauss_table_launch(tab, c->phi, (int)c->n2(), st);
+            g.in = tab;
+        }
+        if (e == cudaSuccess) e = wcrt_launch(g, st);
         if (e == cudaSuccess && two_e) { g.in = e_im; g.out = E1; e = wcrt_launch(g, st); }
     }
     // b = m - INTT(NTT(a) (.) s) + e, fused per row

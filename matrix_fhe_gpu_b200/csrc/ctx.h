@@ -71,6 +71,8 @@ struct WcrtArgs {
     int lz0 = 0, lzn = 0;                  // relative limb window of one launch (set by wcrt_launch)
 };
 cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st);
+// kSrcGauss input: int8 noise value of every logical coefficient [phi][cols]
+cudaError_t gauss_table_launch(signed char* out, int phi, int cols, cudaStream_t st);
 
 // ---- fp64 complex kernels (fp64ops.cu) --------------------------------------------------------------
 // out[o][col] = sum_i tab[i][o] * in[i][col], phi x phi table, cols columns

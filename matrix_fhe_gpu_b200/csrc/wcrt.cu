@@ -52,12 +52,23 @@ __device__ __forceinline__ void load_in4(const WcrtArgs& a, int i, int l, int c,
 #pragma unroll
         for (int j = 0; j < 4; ++j) v[j] = uniform_value(base + j, q, mu_hi);
     } else {
+        const char4 z4 = *reinterpret_cast<const char4*>((const signed char*)a.in + (size_t)i * a.cols + c);
+        const int z[4] = {z4.x, z4.y, z4.z, z4.w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const long long z = gaussian_noise_value((u64)i * a.cols + c + j);
-            v[j] = z >= 0 ? (u64)z : q - (u64)(-z);
-        }
+        for (int j = 0; j < 4; ++j) v[j] = z[j] >= 0 ? (u64)z[j] : q - (u64)(-z[j]);
     }
+}
+
+// centred gaussian noise of every logical coefficient [phi][cols] as int8 (|z| <= 28 by construction:
+// 3.2 * sqrt(-2 ln 2^-53) = 27.4), computed once instead of once per limb and tile
+__global__ void gauss_table_kernel(signed char* __restrict__ out, size_t total) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < total) out[i] = (signed char)gaussian_noise_value((u64)i);
+}
+cudaError_t gauss_table_launch(signed char* out, int phi, int cols, cudaStream_t st) {
+    const size_t total = (size_t)phi * cols;
+    gauss_table_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(out, total);
+    return cudaGetLastError();
 }
 
 template <int SRC, bool SPLIT>

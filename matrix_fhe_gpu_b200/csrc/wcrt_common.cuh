@@ -47,7 +47,9 @@ __device__ __forceinline__ u64 wcrt_load_one(const WcrtArgs& a, int i, int l, in
     } else if constexpr (SRC == kSrcUniform) {
         return uniform_value(((u64)i * a.limbs + l) * a.cols + c, q, mu_hi);
     } else {
-        const long long z = gaussian_noise_value((u64)i * a.cols + c);
+        // kSrcGauss: a.in is the int8 table of centred noise values [phi][cols] (gauss_table_launch); the
+        // reference draws ONE value per logical coefficient and uses it in every limb (HE.cu:590-627)
+        const int z = ((const signed char*)a.in)[(size_t)i * a.cols + c];
         return z >= 0 ? (u64)z : q - (u64)(-z);
     }
 }
