@@ -60,7 +60,7 @@ wdft_gemm_kernel(const double2* __restrict__ tab, const void* __restrict__ in0, 
         for (int k = 0; k < DTK; ++k) {
             double2 a[4], b[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) { a[i] = sTab[buf][k][ty * 4 + i]; b[i] = sIn[buf][k][tx * 4 + i]; }
+            for (int i = 0; i < 4; ++i) { a[i] = sTab[buf][k][ty + 16 * i]; b[i] = sIn[buf][k][tx + 16 * i]; }   // lane-contiguous: no bank conflicts
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -74,11 +74,11 @@ wdft_gemm_kernel(const double2* __restrict__ tab, const void* __restrict__ in0, 
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const int o = o0 + ty * 4 + i;
+        const int o = o0 + ty + 16 * i;
         if (o >= phi) continue;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const int c = c0 + tx * 4 + j;
+            const int c = c0 + tx + 16 * j;
             if (c >= cols) continue;
             const size_t off = (size_t)o * cols + c;
             if (OUT == 0) ((double2*)out0)[off] = make_double2(ar[i][j], ai[i][j]);
@@ -106,43 +106,79 @@ __device__ __forceinline__ double2 cfma(double2 a, double2 b, double2 c) {
     c.y = fma(a.x, b.y, c.y); c.y = fma(a.y, b.x, c.y);
     return c;
 }
+// One CTA per lane, 256 threads as 16 x 16; thread (ty, tx) owns the R x R outputs (ty + 16 i, tx + 16 j), R = n / 16.
+// T = A * M with M in shared memory and A streamed through the read-only path (it is the same n x n matrix for
+// every lane, so it stays in L1/L2); out = T * B likewise.  R^2 complex FMAs per 2R loads.
+template <int R>
 __global__ void __launch_bounds__(256)
 xy_sandwich_kernel(const double2* __restrict__ A, const double2* __restrict__ B, const double2* __restrict__ in,
-                   double2* __restrict__ out, int n) {
+                   double2* __restrict__ out) {
+    constexpr int n = 16 * R;
     extern __shared__ __align__(16) double2 sm_xy[];
     double2* sM = sm_xy;                 // [n][n] the lane's matrix
-    double2* sT = sm_xy + (size_t)n * n; // [n][n] A * M
-    const size_t nn = (size_t)n * n;
-    const double2* M = in + (size_t)blockIdx.x * nn;
-    for (size_t i = threadIdx.x; i < nn; i += blockDim.x) sM[i] = M[i];
+    double2* sT = sm_xy + n * n;         // [n][n] A * M
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const double2* M = in + (size_t)blockIdx.x * n * n;
+    for (int i = threadIdx.x; i < n * n; i += 256) sM[i] = M[i];
     __syncthreads();
-    for (size_t idx = threadIdx.x; idx < nn; idx += blockDim.x) {
-        const int r = (int)(idx / n), c = (int)(idx % n);
-        double2 acc = make_double2(0, 0);
-        for (int k = 0; k < n; ++k) acc = cfma(__ldg(A + (size_t)r * n + k), sM[(size_t)k * n + c], acc);
-        sT[idx] = acc;
+    double2 acc[R][R];
+#pragma unroll
+    for (int i = 0; i < R; ++i)
+#pragma unroll
+        for (int j = 0; j < R; ++j) acc[i][j] = make_double2(0, 0);
+#pragma unroll 4
+    for (int k = 0; k < n; ++k) {
+        double2 a[R], b[R];
+#pragma unroll
+        for (int i = 0; i < R; ++i) { a[i] = __ldg(A + (ty + 16 * i) * n + k); b[i] = sM[k * n + tx + 16 * i]; }
+#pragma unroll
+        for (int i = 0; i < R; ++i)
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc[i][j] = cfma(a[i], b[j], acc[i][j]);
     }
+#pragma unroll
+    for (int i = 0; i < R; ++i)
+#pragma unroll
+        for (int j = 0; j < R; ++j) { sT[(ty + 16 * i) * n + tx + 16 * j] = acc[i][j]; acc[i][j] = make_double2(0, 0); }
     __syncthreads();
-    double2* O = out + (size_t)blockIdx.x * nn;
-    for (size_t idx = threadIdx.x; idx < nn; idx += blockDim.x) {
-        const int r = (int)(idx / n), c = (int)(idx % n);
-        double2 acc = make_double2(0, 0);
-        for (int k = 0; k < n; ++k) acc = cfma(sT[(size_t)r * n + k], __ldg(B + (size_t)k * n + c), acc);
-        O[idx] = acc;
+#pragma unroll 4
+    for (int k = 0; k < n; ++k) {
+        double2 a[R], b[R];
+#pragma unroll
+        for (int i = 0; i < R; ++i) { a[i] = sT[(ty + 16 * i) * n + k]; b[i] = __ldg(B + k * n + tx + 16 * i); }
+#pragma unroll
+        for (int i = 0; i < R; ++i)
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc[i][j] = cfma(a[i], b[j], acc[i][j]);
     }
+    double2* O = out + (size_t)blockIdx.x * n * n;
+#pragma unroll
+    for (int i = 0; i < R; ++i)
+#pragma unroll
+        for (int j = 0; j < R; ++j) O[(ty + 16 * i) * n + tx + 16 * j] = acc[i][j];
 }
-cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,
-                               cudaStream_t st) {
-    const size_t smem = 2 * (size_t)n * n * sizeof(double2);
+template <int R>
+static cudaError_t xy_sandwich_launch_r(const double2* A, const double2* B, const double2* in, double2* out, int lanes,
+                                        cudaStream_t st) {
+    constexpr int n = 16 * R;
+    constexpr size_t smem = 2 * (size_t)n * n * sizeof(double2);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(xy_sandwich_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(xy_sandwich_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    if (smem > 200 * 1024) return cudaErrorInvalidValue;
-    xy_sandwich_kernel<<<lanes, 256, smem, st>>>(A, B, in, out, n);
+    xy_sandwich_kernel<R><<<lanes, 256, smem, st>>>(A, B, in, out);
     return cudaGetLastError();
+}
+cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,
+                               cudaStream_t st) {
+    switch (n) {
+        case 16: return xy_sandwich_launch_r<1>(A, B, in, out, lanes, st);
+        case 32: return xy_sandwich_launch_r<2>(A, B, in, out, lanes, st);
+        case 64: return xy_sandwich_launch_r<4>(A, B, in, out, lanes, st);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 __global__ void matmul_complex_kernel(const double2* A, const double2* B, double2* C, int n) {
