@@ -86,6 +86,23 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2):
         err = float((dec - m).abs().max())
         assert err < 1e-3, err
         if L == 11:
+            # the W-CRT alone: a dense modular GEMM on the tcgen05 tensor cores (int8 digit planes, TMEM accumulators)
+            a_u = g.sample_uniform()
+            ms_w = timed(lambda: g.wntt_forward_matrix(a_u), 10)
+            nd = [(int(q).bit_length() + 7) // 8 for q in mods]
+            macs8 = sum(d * d for d in nd) * g.phi * g.phi * g.n2
+            try:
+                bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+                peak8, src = 2.0 * bf16 * 1e12 / 2.0, "2 x measured bf16 MAC rate (MEASURED_PEAKS.json; int8 is nominally twice bf16)"
+            except Exception:
+                peak8, src = 2.25e15, "nominal 4.5 Pop/s int8 dense"
+            out["wcrt_forward_L11"] = {"ms": ms_w, "modular_macs_per_s": g.phi * g.phi * L * g.n2 / (ms_w * 1e-3),
+                                       "int8_macs_per_s": macs8 / (ms_w * 1e-3),
+                                       "roofline": {"bound": "tensor", "achieved": 2e-12 * macs8 / (ms_w * 1e-3),
+                                                    "peak": 2e-12 * peak8, "unit": "Top/s (int8)",
+                                                    "frac": macs8 / (ms_w * 1e-3) / peak8, "peak_source": src},
+                                       "kernel": "wcrt_umma_kernel (tcgen05.mma kind::i8), profiles/r1_07_ncu_umma_summary.txt"}
+            del a_u
             zero = torch.zeros_like(sk)
             ct_r, ct_i = g.allocate_ciphertext(), g.allocate_ciphertext()
 
