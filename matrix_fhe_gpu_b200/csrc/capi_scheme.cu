@@ -40,13 +40,21 @@ WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
     a.tabt = inverse ? c->d_wdigt_inv : c->d_wdigt_fwd;
     return a;
 }
+WdftTab wdft_tab(const mfhe_ctx* c, bool inverse) {
+    WdftTab w;
+    w.full = inverse ? c->d_wdft_inv : c->d_wdft_fwd;
+    w.half = inverse ? c->d_wdfth_inv : c->d_wdfth_fwd;
+    w.pairs = c->d_wpairs;
+    w.mode = c->wdft_generic ? 0 : (inverse ? 2 : 1);
+    return w;
+}
 
 }  // namespace
 
 extern "C" void mfhe_ctx_destroy(mfhe_ctx* c) {
     if (!c) return;
     cudaFree(c->d_moduli); cudaFree(c->d_mu); cudaFree(c->d_wtab_fwd); cudaFree(c->d_wtab_inv); cudaFree(c->d_wdig_fwd); cudaFree(c->d_wdig_inv); cudaFree(c->d_wdigt_fwd); cudaFree(c->d_wdigt_inv);
-    cudaFree(c->d_wdft_fwd); cudaFree(c->d_wdft_inv);
+    cudaFree(c->d_wdft_fwd); cudaFree(c->d_wdft_inv); cudaFree(c->d_wpairs); cudaFree(c->d_wdfth_fwd); cudaFree(c->d_wdfth_inv);
     cudaFree(c->d_xyV); cudaFree(c->d_xyVT); cudaFree(c->d_xyVinv); cudaFree(c->d_xyVinvT);
     cudaFree(c->d_crt_Q); cudaFree(c->d_crt_Qhalf); cudaFree(c->d_crt_M); cudaFree(c->d_crt_inv);
     cudaFree(c->arena);
@@ -147,6 +155,29 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     std::vector<host::cplx> wf(pp), wi(pp);
     for (size_t i = 0; i < phi; ++i)
         for (size_t o = 0; o < phi; ++o) { wf[i * phi + o] = wV[o * phi + i]; wi[i * phi + o] = wVinv[o * phi + i]; }
+    // conjugate pairs of lanes: exponents e and p - e (both units); representative = the smaller lane index
+    std::vector<int2> wpairs;
+    {
+        std::vector<int> at(c->p, -1);
+        for (size_t w = 0; w < phi; ++w) at[c->wexp[w]] = (int)w;
+        std::vector<char> seen(phi, 0);
+        for (size_t w = 0; w < phi; ++w) {
+            if (seen[w]) continue;
+            const int w2 = at[c->p - c->wexp[w]];
+            if (w2 < 0 || (size_t)w2 == w || seen[w2]) { wpairs.clear(); break; }
+            seen[w] = seen[w2] = 1;
+            wpairs.push_back(make_int2((int)w, w2));
+        }
+        if (wpairs.size() * 2 != phi) wpairs.clear();
+    }
+    const size_t hp = wpairs.size();
+    std::vector<host::cplx> whf(phi * hp), whi(phi * hp);
+    for (size_t k = 0; k < hp; ++k)
+        for (size_t r = 0; r < phi; ++r) {
+            whf[r * hp + k] = wf[r * phi + wpairs[k].x];          // [i = r][pair]
+            whi[k * phi + r] = wi[(size_t)wpairs[k].x * phi + r];  // [pair][o = r]
+        }
+    c->wdft_generic = (hp == 0 || std::getenv("MFHE_WDFT_GENERIC")) ? 1 : 0;
     const size_t nn = (size_t)n * n;
     std::vector<host::cplx> xVT(nn), xVinvT(nn);
     for (int r = 0; r < n; ++r)
@@ -156,6 +187,7 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
 #define UP(dst, vec) if (e == cudaSuccess) e = upload(dst, (vec).data(), (vec).size() * sizeof((vec)[0]))
     UP(c->d_moduli, c->moduli); UP(c->d_mu, mu); UP(c->d_wtab_fwd, tab_fwd); UP(c->d_wtab_inv, tab_inv);
     UP(c->d_wdft_fwd, wf); UP(c->d_wdft_inv, wi);
+    if (hp) { UP(c->d_wpairs, wpairs); UP(c->d_wdfth_fwd, whf); UP(c->d_wdfth_inv, whi); }
     if (want_digits) { UP(c->d_wdig_fwd, dig_fwd); UP(c->d_wdig_inv, dig_inv); }
     if (want_tiles) { UP(c->d_wdigt_fwd, digt_fwd); UP(c->d_wdigt_inv, digt_inv); }
     UP(c->d_xyV, xV); UP(c->d_xyVT, xVT); UP(c->d_xyVinv, xVinv); UP(c->d_xyVinvT, xVinvT);
@@ -259,19 +291,19 @@ extern "C" int mfhe_layout_convert(mfhe_ctx* c, const uint64_t* in, uint64_t* ou
 // ---- complex W-DFT ------------------------------------------------------------------------------------
 extern "C" int mfhe_wdft_forward_complex(mfhe_ctx* c, const double* in, double* out, void* s) {
     if (!c || !in || !out || in == out) return fail(MFHE_EINVAL, "wdft_forward_complex: bad argument");
-    return done(wdft_launch(c->d_wdft_fwd, (const double2*)in, (double2*)out, c->phi, (int)c->n2(), S(s)), "wdft_forward_complex");
+    return done(wdft_launch(wdft_tab(c, false), (const double2*)in, (double2*)out, c->phi, (int)c->n2(), S(s)), "wdft_forward_complex");
 }
 extern "C" int mfhe_wdft_inverse_complex(mfhe_ctx* c, const double* in, double* out, void* s) {
     if (!c || !in || !out || in == out) return fail(MFHE_EINVAL, "wdft_inverse_complex: bad argument");
-    return done(wdft_launch(c->d_wdft_inv, (const double2*)in, (double2*)out, c->phi, (int)c->n2(), S(s)), "wdft_inverse_complex");
+    return done(wdft_launch(wdft_tab(c, true), (const double2*)in, (double2*)out, c->phi, (int)c->n2(), S(s)), "wdft_inverse_complex");
 }
 extern "C" int mfhe_wdft_forward_centered_pair(mfhe_ctx* c, const int64_t* re, const int64_t* im, double* ore, double* oim, void* s) {
     if (!c || !re || !im || !ore || !oim) return fail(MFHE_EINVAL, "wdft_forward_centered_pair: NULL argument");
-    return done(wdft_pair_launch(c->d_wdft_fwd, re, im, ore, oim, c->phi, (int)c->n2(), 1, S(s)), "wdft_forward_centered_pair");
+    return done(wdft_pair_launch(wdft_tab(c, false), re, im, ore, oim, c->phi, (int)c->n2(), 1, S(s)), "wdft_forward_centered_pair");
 }
 extern "C" int mfhe_wdft_inverse_pair(mfhe_ctx* c, const double* re, const double* im, double* ore, double* oim, void* s) {
     if (!c || !re || !im || !ore || !oim) return fail(MFHE_EINVAL, "wdft_inverse_pair: NULL argument");
-    return done(wdft_pair_launch(c->d_wdft_inv, re, im, ore, oim, c->phi, (int)c->n2(), 0, S(s)), "wdft_inverse_pair");
+    return done(wdft_pair_launch(wdft_tab(c, true), re, im, ore, oim, c->phi, (int)c->n2(), 0, S(s)), "wdft_inverse_pair");
 }
 
 // ---- XY embedding, quantise, CRT ------------------------------------------------------------------------
@@ -329,7 +361,7 @@ extern "C" int mfhe_encode(mfhe_ctx* c, const double* msg, uint64_t* out_re, uin
     cudaStream_t st = S(s);
     // 1) per-lane XY-IDFT, all lanes in one launch   2) complex W-IDFT over the lane axis
     cudaError_t e = xy_sandwich_launch(c->d_xyVinv, c->d_xyVinvT, (const double2*)msg, xy, c->n, c->phi, st);
-    if (e == cudaSuccess) e = wdft_launch(c->d_wdft_inv, xy, wc, c->phi, (int)c->n2(), st);
+    if (e == cudaSuccess) e = wdft_launch(wdft_tab(c, true), xy, wc, c->phi, (int)c->n2(), st);
     // 3+4) quantise inside the W-CRT loader, write the matrix-major result directly
     for (int part = 0; part < 2 && e == cudaSuccess; ++part) {
         WcrtArgs a = wcrt_args(c, false);
@@ -364,7 +396,7 @@ static cudaError_t decode_tail(mfhe_ctx* c, const u64* er, const u64* ei, int la
     }
     // CRT compose + centre + /delta for all lanes in one launch (reference: 1024 launches, HE.cu:1653-1672)
     if (e == cudaSuccess) e = crt_to_complex_launch(crt_dev(c), cr, ci, cc, (int)c->n2(), c->L, c->phi, c->delta, st);
-    if (e == cudaSuccess) e = wdft_launch(c->d_wdft_fwd, cc, ec, c->phi, (int)c->n2(), st);
+    if (e == cudaSuccess) e = wdft_launch(wdft_tab(c, false), cc, ec, c->phi, (int)c->n2(), st);
     if (e == cudaSuccess) e = xy_sandwich_launch(c->d_xyV, c->d_xyVT, ec, out, c->n, c->phi, st);
     return e;
 }

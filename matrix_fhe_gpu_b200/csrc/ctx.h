@@ -29,6 +29,11 @@ struct mfhe_ctx {
     std::vector<int> ndig;                    // [L] ceil(bits(q_l) / 8)
     double2* d_wdft_fwd = nullptr;            // [i = r][o = w]
     double2* d_wdft_inv = nullptr;            // [i = w][o = r]
+    // conjugate-pair form of the same tables (fp64ops.cu): lanes (w, w') with exponents (e, p - e)
+    int2* d_wpairs = nullptr;                 // [phi/2] {w, w'}
+    double2* d_wdfth_fwd = nullptr;           // [i = r][pair]      = d_wdft_fwd[r][w]
+    double2* d_wdfth_inv = nullptr;           // [pair][o = r]      = d_wdft_inv[w][r]
+    int wdft_generic = 0;                     // 1: MFHE_WDFT_GENERIC was set at creation, use the full complex GEMM
     double2 *d_xyV = nullptr, *d_xyVT = nullptr, *d_xyVinv = nullptr, *d_xyVinvT = nullptr;   // [n][n]
     mfhe::u64 *d_crt_Q = nullptr, *d_crt_Qhalf = nullptr, *d_crt_M = nullptr, *d_crt_inv = nullptr;
     mfhe_ntt_plan* xy_plan = nullptr;
@@ -76,9 +81,11 @@ cudaError_t gauss_table_launch(signed char* out, int phi, int cols, cudaStream_t
 
 // ---- fp64 complex kernels (fp64ops.cu) --------------------------------------------------------------
 // out[o][col] = sum_i tab[i][o] * in[i][col], phi x phi table, cols columns
-cudaError_t wdft_launch(const double2* tab, const double2* in, double2* out, int phi, int cols, cudaStream_t st);
+// mode 1: conjugate pairs along the outputs (forward table), 2: along the inputs (inverse), 0: full table only
+struct WdftTab { const double2* full; const double2* half; const int2* pairs; int mode; };
+cudaError_t wdft_launch(const WdftTab& tab, const double2* in, double2* out, int phi, int cols, cudaStream_t st);
 // same on split planes: in = (re, im) of type double (pair = 0) or int64 (pair = 1)
-cudaError_t wdft_pair_launch(const double2* tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
+cudaError_t wdft_pair_launch(const WdftTab& tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
                              int phi, int cols, int int_input, cudaStream_t st);
 // out = A * in * B per lane (A, B n x n), lanes matrices
 cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,

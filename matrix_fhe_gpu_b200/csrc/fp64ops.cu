@@ -87,17 +87,191 @@ wdft_gemm_kernel(const double2* __restrict__ tab, const void* __restrict__ in0, 
     }
 }
 
-cudaError_t wdft_launch(const double2* tab, const double2* in, double2* out, int phi, int cols, cudaStream_t st) {
-    dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
-    wdft_gemm_kernel<0, 0><<<grid, DTHREADS, 0, st>>>(tab, in, nullptr, out, nullptr, phi, cols);
+// ---- conjugate-pair forms: half the DFMAs of the complex GEMM ---------------------------------------------
+// The evaluation points come in conjugate pairs (e, p - e), so the table rows of lanes w, w' are complex
+// conjugates of each other (exactly for V, up to round-off for the Gauss-Jordan inverse, whose COLUMNS pair up).
+// With t = c + i d the table entry of the pair's representative:
+//   forward (pairs along the outputs):  E[w] = (Sca - Sdb) + i (Scb + Sda),  E[w'] = (Sca + Sdb) + i (Scb - Sda)
+//       where Sca = sum c*a etc. over the inputs a + i b              -> 4 real FMAs per (pair, input), not 8;
+//   inverse (pairs along the inputs):   out = sum_pairs c*(x+x') - d*(y-y') + i (c*(y+y') + d*(x-x'))
+//       for the inputs x + i y (lane w) and x' + i y' (lane w')       -> 4 real FMAs per (output, pair).
+template <int IN>
+__device__ __forceinline__ double2 wdft_load(const void* in0, const void* in1, size_t off) {
+    if (IN == 0) return __ldg((const double2*)in0 + off);
+    if (IN == 1) return make_double2(((const double*)in0)[off], ((const double*)in1)[off]);
+    return make_double2((double)((const long long*)in0)[off], (double)((const long long*)in1)[off]);
+}
+template <int OUT>
+__device__ __forceinline__ void wdft_store(void* out0, void* out1, size_t off, double re, double im) {
+    if (OUT == 0) ((double2*)out0)[off] = make_double2(re, im);
+    else { ((double*)out0)[off] = re; ((double*)out1)[off] = im; }
+}
+
+constexpr int PTP = 32;      // forward: pairs per CTA tile (= 64 outputs)
+
+// tabh[i][p] = tab[i][pairs[p].x], hp = phi / 2 pairs; CTA tile = 32 pairs x 64 columns, thread = 2 pairs x 4 columns
+template <int IN, int OUT>
+__global__ void __launch_bounds__(DTHREADS, 2)
+wdft_opair_kernel(const double2* __restrict__ tabh, const int2* __restrict__ pairs, const void* __restrict__ in0,
+                  const void* __restrict__ in1, void* __restrict__ out0, void* __restrict__ out1, int phi, int cols) {
+    __shared__ __align__(16) double2 sTab[2][DTK][PTP];
+    __shared__ __align__(16) double2 sIn[2][DTK][DTC];
+    const int hp = phi >> 1;
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int p0 = blockIdx.y * PTP, c0 = blockIdx.x * DTC;
+    const int lk = t >> 5, lp = t & 31, lg = (t & 31) << 1;
+    double2 rt, ri[2];
+    auto fetch = [&](int k0) {
+        const int i = k0 + lk;
+        rt = (i < phi && p0 + lp < hp) ? __ldg(tabh + (size_t)i * hp + p0 + lp) : make_double2(0, 0);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int c = c0 + lg + j;
+            ri[j] = (i < phi && c < cols) ? wdft_load<IN>(in0, in1, (size_t)i * cols + c) : make_double2(0, 0);
+        }
+    };
+    auto stash = [&](int buf) {
+        sTab[buf][lk][lp] = rt;
+        *reinterpret_cast<double4*>(&sIn[buf][lk][lg]) = make_double4(ri[0].x, ri[0].y, ri[1].x, ri[1].y);
+    };
+    double ca[2][4], cb[2][4], da[2][4], db[2][4];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ca[i][j] = cb[i][j] = da[i][j] = db[i][j] = 0.0;
+    fetch(0); stash(0);
+    __syncthreads();
+    const int ktiles = (phi + DTK - 1) / DTK;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * DTK);
+#pragma unroll
+        for (int k = 0; k < DTK; ++k) {
+            double2 a[2], b[4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) a[i] = sTab[buf][k][ty + 16 * i];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = sIn[buf][k][tx + 16 * j];
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    ca[i][j] = fma(a[i].x, b[j].x, ca[i][j]); cb[i][j] = fma(a[i].x, b[j].y, cb[i][j]);
+                    da[i][j] = fma(a[i].y, b[j].x, da[i][j]); db[i][j] = fma(a[i].y, b[j].y, db[i][j]);
+                }
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int p = p0 + ty + 16 * i;
+        if (p >= hp) continue;
+        const int2 ow = pairs[p];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = c0 + tx + 16 * j;
+            if (c >= cols) continue;
+            wdft_store<OUT>(out0, out1, (size_t)ow.x * cols + c, ca[i][j] - db[i][j], cb[i][j] + da[i][j]);
+            wdft_store<OUT>(out0, out1, (size_t)ow.y * cols + c, ca[i][j] + db[i][j], cb[i][j] - da[i][j]);
+        }
+    }
+}
+
+// tabh[p][o] = tab[pairs[p].x][o]; CTA tile = 64 outputs x 64 columns, thread = 4 x 4, K runs over the hp pairs
+// in steps of IKT = 4 (one table entry and one input pair per thread per step keeps the kernel at 128 registers,
+// two CTAs per SM)
+constexpr int IKT = 4;
+template <int IN, int OUT>
+__global__ void __launch_bounds__(DTHREADS, 2)
+wdft_ipair_kernel(const double2* __restrict__ tabh, const int2* __restrict__ pairs, const void* __restrict__ in0,
+                  const void* __restrict__ in1, void* __restrict__ out0, void* __restrict__ out1, int phi, int cols) {
+    __shared__ __align__(16) double2 sTab[2][IKT][DTO];
+    __shared__ __align__(16) double2 sS[2][IKT][DTC];      // (x + x', -(y - y'))
+    __shared__ __align__(16) double2 sD[2][IKT][DTC];      // (y + y',   x - x')
+    const int hp = phi >> 1;
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int o0 = blockIdx.y * DTO, c0 = blockIdx.x * DTC;
+    const int lk = t >> 6, lg = t & 63;
+    double2 rt, rs, rd;
+    auto fetch = [&](int k0) {
+        const int p = k0 + lk;
+        rt = (p < hp && o0 + lg < phi) ? __ldg(tabh + (size_t)p * phi + o0 + lg) : make_double2(0, 0);
+        const int c = c0 + lg;
+        if (p < hp && c < cols) {
+            const int2 ww = pairs[p];
+            const double2 z = wdft_load<IN>(in0, in1, (size_t)ww.x * cols + c);
+            const double2 w = wdft_load<IN>(in0, in1, (size_t)ww.y * cols + c);
+            rs = make_double2(z.x + w.x, w.y - z.y);
+            rd = make_double2(z.y + w.y, z.x - w.x);
+        } else rs = rd = make_double2(0, 0);
+    };
+    auto stash = [&](int buf) { sTab[buf][lk][lg] = rt; sS[buf][lk][lg] = rs; sD[buf][lk][lg] = rd; };
+    double ar[4][4], ai[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) ar[i][j] = ai[i][j] = 0.0;
+    fetch(0); stash(0);
+    __syncthreads();
+    const int ktiles = (hp + IKT - 1) / IKT;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * IKT);
+#pragma unroll
+        for (int k = 0; k < IKT; ++k) {
+            double2 a[4], s[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = sTab[buf][k][ty + 16 * i]; s[i] = sS[buf][k][tx + 16 * i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { ar[i][j] = fma(a[i].x, s[j].x, ar[i][j]); ar[i][j] = fma(a[i].y, s[j].y, ar[i][j]); }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) s[i] = sD[buf][k][tx + 16 * i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { ai[i][j] = fma(a[i].x, s[j].x, ai[i][j]); ai[i][j] = fma(a[i].y, s[j].y, ai[i][j]); }
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int o = o0 + ty + 16 * i;
+        if (o >= phi) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = c0 + tx + 16 * j;
+            if (c < cols) wdft_store<OUT>(out0, out1, (size_t)o * cols + c, ar[i][j], ai[i][j]);
+        }
+    }
+}
+
+template <int IN, int OUT>
+static cudaError_t wdft_dispatch(const WdftTab& w, const void* in0, const void* in1, void* out0, void* out1, int phi,
+                                 int cols, cudaStream_t st) {
+    const int hp = phi / 2;
+    if (w.mode == 1 && w.half && w.pairs) {
+        dim3 grid((cols + DTC - 1) / DTC, (hp + PTP - 1) / PTP);
+        wdft_opair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+    } else if (w.mode == 2 && w.half && w.pairs) {
+        dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
+        wdft_ipair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+    } else {
+        dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
+        wdft_gemm_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.full, in0, in1, out0, out1, phi, cols);
+    }
     return cudaGetLastError();
 }
-cudaError_t wdft_pair_launch(const double2* tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
+cudaError_t wdft_launch(const WdftTab& w, const double2* in, double2* out, int phi, int cols, cudaStream_t st) {
+    return wdft_dispatch<0, 0>(w, in, nullptr, out, nullptr, phi, cols, st);
+}
+cudaError_t wdft_pair_launch(const WdftTab& w, const void* in_re, const void* in_im, double* out_re, double* out_im,
                              int phi, int cols, int int_input, cudaStream_t st) {
-    dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
-    if (int_input) wdft_gemm_kernel<2, 1><<<grid, DTHREADS, 0, st>>>(tab, in_re, in_im, out_re, out_im, phi, cols);
-    else           wdft_gemm_kernel<1, 1><<<grid, DTHREADS, 0, st>>>(tab, in_re, in_im, out_re, out_im, phi, cols);
-    return cudaGetLastError();
+    return int_input ? wdft_dispatch<2, 1>(w, in_re, in_im, out_re, out_im, phi, cols, st)
+                     : wdft_dispatch<1, 1>(w, in_re, in_im, out_re, out_im, phi, cols, st);
 }
 
 // ---- out = A * M * B per lane ---------------------------------------------------------------------
