@@ -27,7 +27,10 @@ inline cudaStream_t S(void* s) { return (cudaStream_t)s; }
 inline int done(cudaError_t e, const char* where) { return e == cudaSuccess ? MFHE_OK : cuda_fail(e, where); }
 
 CrtDev crt_dev(const mfhe_ctx* c) {
-    return CrtDev{c->d_crt_Q, c->d_crt_Qhalf, c->d_crt_M, c->d_crt_inv, c->d_moduli, c->d_mu, c->W};
+    CrtDev d{c->d_crt_Q, c->d_crt_Qhalf, c->d_crt_M, c->d_crt_inv, c->d_moduli, c->d_mu, c->W, c->crt_fast, c->L, c->crt_ginv,
+             c->crt_Q2lo, c->crt_Q2hi, 0, 0};
+    d.H2lo = (c->crt_Q2lo >> 1) | (c->crt_Q2hi << 63); d.H2hi = c->crt_Q2hi >> 1;
+    return d;
 }
 
 WcrtArgs wcrt_args(const mfhe_ctx* c, bool inverse) {
@@ -148,6 +151,14 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     } catch (const std::exception& e) {
         delete c;
         return fail(MFHE_EINVAL, std::string("ctx_create: ") + e.what());
+    }
+    if (L >= 2 && c->moduli[0] != c->moduli[1] && !std::getenv("MFHE_CRT_FULL")) {
+        const unsigned __int128 q01 = (unsigned __int128)c->moduli[0] * c->moduli[1];
+        if (!(q01 >> 126)) {
+            c->crt_fast = 1;
+            c->crt_ginv = host::invmod(c->moduli[0] % c->moduli[1], c->moduli[1]);
+            c->crt_Q2lo = (uint64_t)q01; c->crt_Q2hi = (uint64_t)(q01 >> 64);
+        }
     }
     c->W = crt.words; c->hQ = crt.Q; c->hQhalf = crt.Qhalf; c->hM = crt.M; c->hInv = crt.inv;
 

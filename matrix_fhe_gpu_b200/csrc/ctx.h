@@ -33,6 +33,7 @@ struct mfhe_ctx {
     int2* d_wpairs = nullptr;                 // [phi/2] {w, w'}
     double2* d_wdfth_fwd = nullptr;           // [i = r][pair]      = d_wdft_fwd[r][w]
     double2* d_wdfth_inv = nullptr;           // [pair][o = r]      = d_wdft_inv[w][r]
+    int crt_fast = 0; mfhe::u64 crt_ginv = 0, crt_Q2lo = 0, crt_Q2hi = 0;     // see CrtDev
     int wdft_generic = 0;                     // 1: MFHE_WDFT_GENERIC was set at creation, use the full complex GEMM
     double2 *d_xyV = nullptr, *d_xyVT = nullptr, *d_xyVinv = nullptr, *d_xyVinvT = nullptr;   // [n][n]
     mfhe::u64 *d_crt_Q = nullptr, *d_crt_Qhalf = nullptr, *d_crt_M = nullptr, *d_crt_inv = nullptr;
@@ -95,7 +96,11 @@ cudaError_t quantize_launch(const double2* in, u64* re, u64* im, const u64* modu
                             int limbs, int lanes, double delta, cudaStream_t st);
 
 // ---- CRT compose (crt.cu) ----------------------------------------------------------------------------
-struct CrtDev { const u64 *Q, *Qhalf, *M, *inv, *moduli; const ulonglong2* mu; int W; };
+struct CrtDev {
+    const u64 *Q, *Qhalf, *M, *inv, *moduli; const ulonglong2* mu; int W;
+    // two-limb fast path of crt_to_complex (crt.cu: crt_small): q0^-1 mod q1, q0 q1 and floor(q0 q1 / 2)
+    int fast, L; u64 ginv, Q2lo, Q2hi, H2lo, H2hi;     // fast path only when all L limbs are composed
+};
 cudaError_t crt_compose_big_launch(const CrtDev& c, const u64* in, u64* mag, uint8_t* neg, int n2, int limbs, int lanes,
                                    int lane_stride_limbs, cudaStream_t st);
 cudaError_t crt_compose_i64_launch(const CrtDev& c, const u64* in, long long* out, int n2, int limbs, int lanes,

@@ -191,6 +191,28 @@ def test_quantize_and_crt_bit_exact(S, cuda_device, name):
     assert (host(c) == oc).all()
     re, im = x.reshape(o.phi, -1)[0], x.reshape(o.phi, -1)[1]
     assert (host(g.dequantize_exact(dev(re, cuda_device), dev(im, cuda_device))) == o.dequantize_exact(re, im)).all()
+    # the two-limb fast path of crt_to_complex (crt.cu: crt_small) and its fall-back, mixed in one launch: small
+    # values of both signs, the edges of (-q0 q1 / 2, q0 q1 / 2), and arbitrary residues -- the fp64 image must
+    # equal the full composition's bit for bit
+    if o.L >= 2:
+        q01 = int(o.moduli[0]) * int(o.moduli[1])
+        vals = [0, 1, -1, 2 ** 63, -2 ** 63, 2 ** 64 - 1, 2 ** 64, -(2 ** 64) - 5, q01 // 2, -(q01 // 2), q01 // 2 + 1,
+                -(q01 // 2) - 1, q01 - 1, q01, int(o.moduli[0]), -int(o.moduli[1])]
+        vals += [int(v) for v in rng.integers(-2 ** 62, 2 ** 62, size=o.n2 // 2)]
+        Q = 1
+        for q in o.moduli:
+            Q *= int(q)
+        vals = [v for v in vals if abs(v) < Q // 2][: o.n2]
+        mixed = res.reshape(o.L, o.n2).copy()
+        for i, v in enumerate(vals):
+            for k in range(o.L):
+                mixed[k, i] = v % int(o.moduli[k])
+        re = mixed.reshape(-1)
+        im = np.ascontiguousarray(mixed[:, ::-1]).reshape(-1)
+        got = host(g.dequantize_exact(dev(re, cuda_device), dev(im, cuda_device)))
+        assert (got == o.dequantize_exact(re, im)).all()
+        for i, v in enumerate(vals[:16]):
+            assert got[i].real == float(np.float64(v) / o.delta) or abs(v) >= 2 ** 53
 
 
 def message(o, kind, seed=7):
