@@ -373,11 +373,16 @@ extern "C" int mfhe_encode(mfhe_ctx* c, const double* msg, uint64_t* out_re, uin
     // 1) per-lane XY-IDFT, all lanes in one launch   2) complex W-IDFT over the lane axis
     cudaError_t e = xy_sandwich_launch(c->d_xyVinv, c->d_xyVinvT, (const double2*)msg, xy, c->n, c->phi, st);
     if (e == cudaSuccess) e = wdft_launch(wdft_tab(c, true), xy, wc, c->phi, (int)c->n2(), st);
-    // 3+4) quantise inside the W-CRT loader, write the matrix-major result directly
+    // 3) llround(z * delta) once per value into two int64 planes (they reuse the xy buffer, dead by now)
+    // 4) W-CRT with the signed-integer loader (value mod q_l per limb), matrix-major result written directly
+    const size_t total = (size_t)c->phi * c->n2();
+    long long* qre = (long long*)xy;
+    long long* qim = qre + total;
+    if (e == cudaSuccess) e = llround_planes_launch(wc, qre, qim, total, c->delta, st);
     for (int part = 0; part < 2 && e == cudaSuccess; ++part) {
         WcrtArgs a = wcrt_args(c, false);
-        a.in = wc; a.out = (u64*)(part ? out_im : out_re);
-        a.source = part ? kSrcQuantIm : kSrcQuantRe; a.out_layout = MFHE_LAYOUT_MATRIX;
+        a.in = part ? qim : qre; a.out = (u64*)(part ? out_im : out_re);
+        a.source = kSrcI64; a.out_layout = MFHE_LAYOUT_MATRIX;
         e = wcrt_launch(a, st);
     }
     return done(e, "encode");

@@ -88,6 +88,8 @@ cudaError_t wdft_launch(const WdftTab& tab, const double2* in, double2* out, int
 // same on split planes: in = (re, im) of type double (pair = 0) or int64 (pair = 1)
 cudaError_t wdft_pair_launch(const WdftTab& tab, const void* in_re, const void* in_im, double* out_re, double* out_im,
                              int phi, int cols, int int_input, cudaStream_t st);
+// (re, im)[i] = llround(in[i] * delta) as int64 planes (total even or odd, 16-byte aligned buffers)
+cudaError_t llround_planes_launch(const double2* in, long long* re, long long* im, size_t total, double delta, cudaStream_t st);
 // out = A * in * B per lane (A, B n x n), lanes matrices
 cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2* in, double2* out, int n, int lanes,
                                cudaStream_t st);

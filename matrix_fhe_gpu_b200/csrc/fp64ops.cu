@@ -274,6 +274,25 @@ cudaError_t wdft_pair_launch(const WdftTab& w, const void* in_re, const void* in
                      : wdft_dispatch<1, 1>(w, in_re, in_im, out_re, out_im, phi, cols, st);
 }
 
+// llround(z * delta) of both parts of every complex value, once, as two int64 planes: the W-CRT loader then only
+// reduces them modulo each limb (signed_mod) instead of converting the same double in every limb.
+__global__ void llround_planes_kernel(const double2* __restrict__ in, long long* __restrict__ re, long long* __restrict__ im,
+                                      size_t total, double delta) {
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    if (i + 1 < total) {
+        const double4 z = *reinterpret_cast<const double4*>(in + i);
+        *reinterpret_cast<longlong2*>(re + i) = make_longlong2(llround(z.x * delta), llround(z.z * delta));
+        *reinterpret_cast<longlong2*>(im + i) = make_longlong2(llround(z.y * delta), llround(z.w * delta));
+    } else if (i < total) {
+        const double2 z = in[i];
+        re[i] = llround(z.x * delta); im[i] = llround(z.y * delta);
+    }
+}
+cudaError_t llround_planes_launch(const double2* in, long long* re, long long* im, size_t total, double delta, cudaStream_t st) {
+    llround_planes_kernel<<<(unsigned)((total / 2 + 256) / 256), 256, 0, st>>>(in, re, im, total, delta);
+    return cudaGetLastError();
+}
+
 // ---- out = A * M * B per lane ---------------------------------------------------------------------
 __device__ __forceinline__ double2 cfma(double2 a, double2 b, double2 c) {
     c.x = fma(a.x, b.x, c.x); c.x = fma(-a.y, b.y, c.x);
