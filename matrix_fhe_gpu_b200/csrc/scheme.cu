@@ -21,8 +21,11 @@ __device__ __forceinline__ size_t row_offset(int layout, u32 w, u32 l, u32 y, in
     return layout == MFHE_LAYOUT_POLY ? (((size_t)w * n + y) * L + l) * n : (((size_t)w * L + l) * n + y) * n;
 }
 
+#ifndef MFHE_XROW_MINB
+#define MFHE_XROW_MINB 4
+#endif
 template <int LOGN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, MFHE_XROW_MINB)
 xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_tab, size_t rows) {
     using Net = SmallNet<LOGN>;
     constexpr int TPP = Net::TPP, PPB = 256 / TPP, STRIDE = Net::STRIDE;

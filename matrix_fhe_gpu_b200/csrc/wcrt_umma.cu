@@ -83,6 +83,13 @@ __device__ __forceinline__ void tmem_ld4(u32 taddr, u32 (&r)[4]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
 }
+// 16 lanes x 256 bits: thread T gets lane T/4 (r0, r1) and lane T/4 + 8 (r2, r3), columns 2 (T%4), 2 (T%4) + 1 of the
+// 8-column group (cute Copy_Traits<SM100_TMEM_LOAD_16dp256b1x>): four threads share a row, so the epilogue's
+// 16-byte stores of one instruction form 64-byte row segments instead of 32 scattered 16-byte pieces
+__device__ __forceinline__ void tmem_ld_16x256(u32 taddr, u32 (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
     const u32 z = 0;
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr), "r"(z) : "memory");
@@ -288,14 +295,15 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             }
         }
     } else if (warp >= 8) {
-        // ===== epilogue (8 warps): TMEM lanes 32*(warp%4).. = output rows, column half (warp-8)/4 =====
+        // ===== epilogue (8 warps): TMEM lanes 32*(warp%4).. = output rows, column half (warp-8)/4.  Sub-group sg =
+        // (16-lane half, 8-column group): thread holds rows lane/4 and lane/4 + 8, columns 2 (lane%4) + {0, 1} =====
         const u32 tlane = tmem + ((u32)(32 * (warp & 3)) << 16);
         for (int it = 0; it < my_tiles; ++it) {
             const TileIdx ti = tile_decode((int)blockIdx.x + it * (int)gridDim.x, nOT, nCB);
             const int lrel = a.lz0 + ti.lz, l = a.limb0 + lrel;
             const u64 q = a.moduli[l];
             const ulonglong2 mu = a.mu[l];
-            const int o = ti.ot * UM + 32 * (warp & 3) + lane;
+            const int o = ti.ot * UM + 32 * (warp & 3) + (lane >> 2);
             mbar_wait(bar_tfull, it & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // phase 1 (holds TMEM): fold the 2ND-1 partial sums of each of this thread's 16 outputs into
@@ -308,7 +316,8 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             for (int sg = 0; sg < 4; ++sg) {
                 u32 acc[2 * ND - 1][4];
 #pragma unroll
-                for (int w = 0; w < 2 * ND - 1; ++w) tmem_ld4(tlane + (u32)(w * UN + ccol + 4 * sg), acc[w]);
+                for (int w = 0; w < 2 * ND - 1; ++w)
+                    tmem_ld_16x256(tlane + ((u32)(16 * (sg >> 1)) << 16) + (u32)(w * UN + ccol + 8 * (sg & 1)), acc[w]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
@@ -329,7 +338,13 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             if (vlo[0] == 0x12345678u) a.out[0] = vup[1];
             continue;
 #endif
-            // phase 2 (overlaps the next tile's MMAs): value = lo + up * 2^40, one Barrett reduction, 16-byte stores
+            // phase 2 (overlaps the next tile's MMAs): value = lo + up * 2^40, one Barrett reduction, 16-byte stores.
+            // The value is the exact integer sum_i tab*in < phi q^2 < 2^(k+62) (k = bits of q <= 48 here), so a
+            // ONE-word Barrett suffices: qhat = mulhi(v >> (k-2), floor(2^(k+62) / q)) is within 2 of the quotient
+            // (HAC 14.42 with the bounds v / 2^(k+62) < 1/2 and 2^(k-2) / q <= 1/2), r = v - qhat q < 3q.
+            const int kb = 64 - __clzll((long long)q);
+            const u64 mu1 = (mu.y << (kb - 2)) | (mu.x >> (66 - kb));        // floor(2^128 / q) >> (66 - k)
+            const u64 q2 = 2 * q;
 #pragma unroll
             for (int e = 0; e < 16; e += 2) {
                 u64 r[2];
@@ -339,9 +354,13 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                     const u64 lo = vlo[e + k] + x;
                     u64 hi = (vup[e + k] >> 24) + (lo < x);
                     if constexpr (2 * ND - 1 > 10) hi += (u64)vtop[e + k] << 16;
-                    r[k] = reduce128(lo, hi, q, mu.x, mu.y);
+                    const u64 x1 = (lo >> (kb - 2)) | (hi << (66 - kb));
+                    const u64 rr = lo - __umul64hi(x1, mu1) * q;
+                    r[k] = csub(csub(rr, q2), q);
                 }
-                const size_t off = poly_set_addr(a.out_layout, o, lrel, ti.cblk * UN + ccol + e, a.n, a.cols, a.limbs);
+                // e = 4 sg + 2 p: rows o + 16 (sg / 2) + 8 p, column pair 8 (sg % 2) + 2 (lane % 4)
+                const size_t off = poly_set_addr(a.out_layout, o + 16 * (e >> 3) + 8 * ((e >> 1) & 1), lrel,
+                                                 ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3), a.n, a.cols, a.limbs);
                 *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[0], r[1]);
                 if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[0], r[1]);
             }
