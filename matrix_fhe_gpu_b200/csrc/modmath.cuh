@@ -234,6 +234,21 @@ __device__ __forceinline__ u64 reduce128(u64 lo, u64 hi, u64 q, u64 mu_lo, u64 m
     r = csub(r, 2 * q);
     return csub(r, q);
 }
+// One-word Barrett for products of canonical residues (q < 2^62, k = bits of q):
+//   mu1 = floor(2^(k+62) / q) = floor(2^128 / q) >> (66 - k),  qhat = mulhi((a b) >> (k-2), mu1) >= floor(a b / q) - 2
+// (HAC 14.42: the two truncations cost at most a b / 2^(k+62) <= 1/2 and 2^(k-2) / q < 1/2), so r = a b - qhat q < 3q.
+// Two 64x64 high products instead of the four of mul_barrett.
+struct barrett1_t { u64 q, q2, mu1; int sh; };
+__device__ __forceinline__ barrett1_t make_barrett1(u64 q, u64 mu_lo, u64 mu_hi) {
+    const int k = 64 - __clzll((long long)q);
+    return barrett1_t{q, 2 * q, (mu_hi << (k - 2)) | (mu_lo >> (66 - k)), k - 2};
+}
+__device__ __forceinline__ u64 mul_barrett1(u64 a, u64 b, const barrett1_t& c) {
+    const u64 lo = a * b, hi = __umul64hi(a, b);
+    const u64 x1 = (lo >> c.sh) | (hi << (64 - c.sh));
+    const u64 r = lo - __umul64hi(x1, c.mu1) * c.q;
+    return csub(csub(r, c.q2), c.q);
+}
 __device__ __forceinline__ u64 add_mod(u64 a, u64 b, u64 q) { return csub(a + b, q); }
 __device__ __forceinline__ u64 sub_mod(u64 a, u64 b, u64 q) { return csub(a + q - b, q); }
 __device__ __forceinline__ u64 neg_mod(u64 a, u64 q) { return a ? q - a : 0; }

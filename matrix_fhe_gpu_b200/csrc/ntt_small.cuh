@@ -51,6 +51,12 @@ struct SmallNet {
         for (int j = 0; j < 8; ++j) { v[j] = csub(v[j], q2); v[j] = csub(v[j], q); }
     }
 
+    // the value inverse() returns, known before the transform (lets the caller prefetch what it combines with)
+    __device__ static __forceinline__ u32 out_base(u32 u) {
+        if constexpr (PL > 3) return deposit3(u, IP2);
+        else if constexpr (PL > 0) return deposit3(u, IP1);
+        else return 8 * u;
+    }
     // values at network positions 8u .. 8u+7 (< 2q) -> canonical natural-order coefficients;
     // on return v[j] is the coefficient at position  e + (j << PL)  where e is the return value.
     __device__ static __forceinline__ u32 inverse(u64 (&v)[8], u64* sm, u32 u, const tw_t* __restrict__ itw, u64 q,

@@ -24,6 +24,9 @@ __device__ __forceinline__ size_t row_offset(int layout, u32 w, u32 l, u32 y, in
 #ifndef MFHE_XROW_MINB
 #define MFHE_XROW_MINB 4
 #endif
+#ifndef MFHE_XROW_PREFETCH
+#define MFHE_XROW_PREFETCH 0
+#endif
 template <int LOGN>
 __global__ void __launch_bounds__(256, MFHE_XROW_MINB)
 xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_tab, size_t rows) {
@@ -38,15 +41,25 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
     const ulonglong2 mu = mu_tab[l];
     u64* sm = sm_all + pib * STRIDE;
     u64 v[8];
+#if MFHE_XROW_PREFETCH
+    // the first message row is fetched before the transforms so that its latency hides behind them
+    u64 pm[8];
+    {
+        const u64* m = r.m0 + row_offset(r.m_layout, w, l, y, r.n, r.limbs) + Net::out_base(u);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pm[j] = m[j << Net::PL];
+    }
+#endif
     Net::forward(v, r.a + row_offset(r.a_layout, w, l, y, r.n, r.limbs), sm, u, T.tw + ((size_t)l << LOGN), q, q2);
     {
         const u64* s = r.s + ((size_t)wl << LOGN) + 8 * u;      // key is stored in the same bit-reversed order
         const ulonglong2 s0 = __ldg((const ulonglong2*)s), s1 = __ldg((const ulonglong2*)s + 1),
                          s2 = __ldg((const ulonglong2*)s + 2), s3 = __ldg((const ulonglong2*)s + 3);
-        v[0] = mul_barrett(v[0], s0.x, q, mu.x, mu.y); v[1] = mul_barrett(v[1], s0.y, q, mu.x, mu.y);
-        v[2] = mul_barrett(v[2], s1.x, q, mu.x, mu.y); v[3] = mul_barrett(v[3], s1.y, q, mu.x, mu.y);
-        v[4] = mul_barrett(v[4], s2.x, q, mu.x, mu.y); v[5] = mul_barrett(v[5], s2.y, q, mu.x, mu.y);
-        v[6] = mul_barrett(v[6], s3.x, q, mu.x, mu.y); v[7] = mul_barrett(v[7], s3.y, q, mu.x, mu.y);
+        const barrett1_t bc = make_barrett1(q, mu.x, mu.y);
+        v[0] = mul_barrett1(v[0], s0.x, bc); v[1] = mul_barrett1(v[1], s0.y, bc);
+        v[2] = mul_barrett1(v[2], s1.x, bc); v[3] = mul_barrett1(v[3], s1.y, bc);
+        v[4] = mul_barrett1(v[4], s2.x, bc); v[5] = mul_barrett1(v[5], s2.y, bc);
+        v[6] = mul_barrett1(v[6], s3.x, bc); v[7] = mul_barrett1(v[7], s3.y, bc);
     }
     const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)l << LOGN), q, q2, T.ninv[l], T.w1n[l]);
 #pragma unroll
@@ -60,7 +73,11 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const u32 pos = e + (j << Net::PL);
+#if MFHE_XROW_PREFETCH
+            u64 x = comp ? m[mo + pos] : pm[j];
+#else
             u64 x = m[mo + pos];
+#endif
             if (r.subtract) { x = sub_mod(x, v[j], q); if (er) x = add_mod(x, er[eo + pos], q); }
             else x = add_mod(x, v[j], q);
             o[oo + pos] = x;
