@@ -187,10 +187,17 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                                     C::idesc(UN), 0);
                         }
                     } else {
+#ifdef MFHE_UMMA_DBGN      // operand-fetch experiment: every instruction with N = MFHE_UMMA_DBGN (results are garbage)
+#pragma unroll
+                        for (int u = 0; u < ND; ++u)
+                            umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE + ks * 256, 128, 512), bdesc,
+                                    C::idesc(MFHE_UMMA_DBGN), 1);
+#else
 #pragma unroll
                         for (int u = 0; u < ND; ++u)
                             umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE + ks * 256, 128, 512), bdesc,
                                     C::idesc(ND * UN), 1);
+#endif
                     }
                 }
                 umma_commit(bar_empty(s));
