@@ -10,10 +10,11 @@
 // adds a_u b_v into position u+v for every v at once: ND instructions of shape 128 x (32 ND) x 32 per K step
 // instead of ND^2 small ones, and every A tile is read from shared memory once per K step.
 //
-//   PERSISTENT CTAs (one per SM, 17 warps) walk over the 128 (o) x 32 (c) tiles; K (phi) in chunks of 64 through an
+//   PERSISTENT CTAs (one per SM, 21 warps; 17 for ND = 6) walk over the 128 (o) x UN (c) tiles, UN = 48 columns (32 for
+//   ND = 6; written 32 in the formulas above), the last column block of a limb ragged; K (phi) in chunks of 64 through an
 //   NS-stage ring in shared memory that runs on across tile boundaries, so the next tile's operands are
 //   already landing while the current tile is in its epilogue.
-//   warp 16    one thread issues the tcgen05.mma's (commit -> the stage's "empty" barrier, last chunk -> "tmem
+//   last warp  one thread issues the tcgen05.mma's (commit -> the stage's "empty" barrier, last chunk -> "tmem
 //              full") and, while they run, refills the stage released by the previous chunk with table digits:
 //              the table is stored pre-tiled in the UMMA canonical (no-swizzle, K-major, 8 x 16-byte core
 //              matrices) layout, so one 8 KiB cp.async.bulk per digit plane and chunk lands a ready-to-use A
@@ -22,7 +23,7 @@
 //              int64 / quantiser / samplers) -> canonical u64 residues, LDG.128 of two columns x four
 //              consecutive i per item -> PRMT byte transposes -> K-major core matrices, fence.proxy.async,
 //              mbarrier arrive.
-//   warps 8-15 epilogue: wait for the tile's last commit, tcgen05.ld the 2ND-1 partial sums of 8 columns,
+//   warps 8..  epilogue (4 lane quarters x UN/16 column parts): wait for the tile's last commit, tcgen05.ld the 2ND-1 partial sums of 8 columns,
 //              recombine to 128 bits, ONE Barrett reduction per output, 16-byte stores in either layout; TMEM is
 //              handed back to the issuer as soon as the last accumulator column is in registers.  No zero-fill:
 //              the first K step of a tile is issued as overwrite / accumulate pieces.
@@ -36,9 +37,8 @@
 namespace mfhe {
 
 namespace {
-constexpr int UM = 128, UN = 32, UKC = 64, UTHREADS = 544;
+constexpr int UM = 128, UKC = 64;
 constexpr int A_PLANE = UM * UKC;            // 8 KiB: one digit plane of one A chunk
-constexpr int B_PLANE = UN * UKC;            // 2 KiB
 
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(u32 bar, u32 count) {
@@ -97,10 +97,21 @@ __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
 }  // namespace
 
 template <int ND> struct UmmaCfg {
+    // Tile width.  A 128-row kind::i8 instruction costs ~130-160 clk whatever its N (profiles/r1_10_wcrt_limiters.txt,
+    // third series), so the instruction is made as wide as TMEM allows: N' = ND * UN <= 256, (2ND-1) * UN <= 512.
+    static constexpr int UN = (ND >= 6) ? 32 : 48;
+    static constexpr int B_PLANE = UN * UKC;                            // one input digit plane of one chunk
+    static constexpr int NCG = UN / 8;                                  // 8-column groups
+    static constexpr int PROD_ROUNDS = (2 * NCG + 3) / 4;               // producer items per thread and chunk
+    static constexpr int EPI_PARTS = UN / 16;                           // epilogue: 16 columns per warp
+    static constexpr int EPI_WARPS = 4 * EPI_PARTS;
+    static constexpr int ISSUE_WARP = 8 + EPI_WARPS;
+    static constexpr int THREADS = (ISSUE_WARP + 1) * 32;
     static constexpr int NS = (ND <= 5) ? 4 : 3;                       // ring stages
     static constexpr int STAGE = ND * (A_PLANE + B_PLANE);
     static constexpr int SMEM = NS * STAGE + 1024;                      // + barriers / TMEM pointer, alignment slack
     static constexpr int ACC_COLS = (2 * ND - 1) * UN;
+    static_assert(ACC_COLS <= 512 && ND * UN <= 256 && (ND * UN) % 16 == 0 && UN % 16 == 0, "tile width");
     // kind::i8 instruction descriptor: D = s32, A = B = unsigned 8 bit, both K-major, 128 x N
     __host__ __device__ static constexpr u32 idesc(int n) { return (2u << 4) | ((u32)(n >> 3) << 17) | ((u32)(UM >> 4) << 24); }
 };
@@ -113,9 +124,10 @@ __device__ __forceinline__ TileIdx tile_decode(int tile, int nOT, int nCB) {
 }
 
 template <int SRC, int ND>
-__global__ void __launch_bounds__(UTHREADS, 1)
+__global__ void __launch_bounds__(UmmaCfg<ND>::THREADS, 1)
 wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     using C = UmmaCfg<ND>;
+    constexpr int UN = C::UN, B_PLANE = C::B_PLANE;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
     unsigned char* ctrl = smem + C::NS * C::STAGE;        // barriers: fullA[NS], fullB[NS], empty[NS], tmem_full, tmem_empty
@@ -127,13 +139,13 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     volatile u32* tmem_slot = reinterpret_cast<volatile u32*>(ctrl + 8 * (3 * C::NS + 2));
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int kchunks = a.phi / UKC, nOT = a.phi / UM, nCB = a.cols / UN;
+    const int kchunks = a.phi / UKC, nOT = a.phi / UM, nCB = (a.cols + UN - 1) / UN;     // the last column block may be ragged
     const int my_tiles = (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int my_chunks = my_tiles * kchunks;
 
     if (t == 0) {
         for (int s = 0; s < C::NS; ++s) { mbar_init(bar_fullA(s), 1); mbar_init(bar_fullB(s), 128); mbar_init(bar_empty(s), 1); }
-        mbar_init(bar_tfull, 1); mbar_init(bar_tempty, 8);
+        mbar_init(bar_tfull, 1); mbar_init(bar_tempty, C::EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -146,7 +158,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const u32 tmem = *tmem_slot;
 
-    if (warp == 16) {
+    if (warp == C::ISSUE_WARP) {
         // ===== one thread: issues the MMAs and streams the table digits (one bulk copy per digit plane and chunk) =====
         if (lane == 0) {
             auto issue_A = [&](int g) {
@@ -211,98 +223,111 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
         }
         __syncwarp();
     } else if (warp < 8) {
-        // ===== input-digit producers: two groups of 128 threads take alternate chunks.  Item = (column pair, four
-        // consecutive i): 4 LDG.128, two PRMT byte transposes, K-major core-matrix stores.  The loads of a group's
-        // next chunk (two chunks = one MMA chunk time ahead) are in flight while the current one is converted. =====
+        // ===== input-digit producers: two groups of 128 threads take alternate chunks.  A chunk of one digit stack is
+        // NCG column groups x 2 halves of the 16 four-k groups = 2 NCG warp-items; a lane of a warp-item owns (column
+        // pair, four consecutive i): 4 LDG.128, PRMT byte transposes, K-major core-matrix stores.  One register set
+        // per item: right after an item is converted its registers take the loads of the group's NEXT chunk (two MMA
+        // chunk times ahead), so the loads are in flight while the rest is converted and while the stage is awaited. =====
+        constexpr int R = C::PROD_ROUNDS, WI = 2 * C::NCG;
         const int grp = warp >> 2, pt = t & 127;
-        int ic[2], ikq[2], isw[2];
+        int ic[R], ikq[R], isw[R];
+        bool live[R];
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-            const int id = pt + 128 * r;                           // 256 items per chunk
+        for (int r = 0; r < R; ++r) {
+            const int id = pt + 128 * r, wi = id >> 5;             // warp-item: column group wi % NCG, k half wi / NCG
+            live[r] = wi < WI;
             isw[r] = (id >> 4) & 1;
-            ic[r] = ((id >> 5) & 3) * 8 + (id & 3) * 2;
-            ikq[r] = ((id >> 2) & 3) | (isw[r] << 2) | (((id >> 7) & 1) << 3);
+            ic[r] = (wi % C::NCG) * 8 + (id & 3) * 2;
+            ikq[r] = ((id >> 2) & 3) | (isw[r] << 2) | ((wi / C::NCG) << 3);
         }
         const size_t istride = (size_t)a.limbs * a.cols;
         // fetch-side cursor over this group's chunks
         int f_kt = grp, f_it = 0;
-        size_t f_off[2] = {0, 0};
+        size_t f_off[R];
+        bool f_ok[R];
         int f_lrel = 0, f_l = 0, f_c0 = 0;
         u64 f_q = 0, f_mu = 0;
         auto f_tile = [&]() {
             const TileIdx ti = tile_decode((int)blockIdx.x + f_it * (int)gridDim.x, nOT, nCB);
             f_lrel = a.lz0 + ti.lz; f_l = a.limb0 + f_lrel; f_c0 = ti.cblk * UN;
-            if constexpr (SRC == kSrcMem) {
 #pragma unroll
-                for (int r = 0; r < 2; ++r) f_off[r] = poly_set_addr(a.in_layout, 0, f_lrel, f_c0 + ic[r], a.n, a.cols, a.limbs);
-            } else { f_q = a.moduli[f_l]; f_mu = a.mu[f_l].y; }
+            for (int r = 0; r < R; ++r) {
+                f_ok[r] = live[r] && f_c0 + ic[r] < a.cols;        // ragged last column block: zeros, no loads
+                f_off[r] = 0;
+                if constexpr (SRC == kSrcMem)
+                    if (f_ok[r]) f_off[r] = poly_set_addr(a.in_layout, 0, f_lrel, f_c0 + ic[r], a.n, a.cols, a.limbs);
+            }
+            if constexpr (SRC != kSrcMem) { f_q = a.moduli[f_l]; f_mu = a.mu[f_l].y; }
         };
-        auto fetch = [&](u64 (&rb)[2][8]) {
-            if (f_kt == grp) f_tile();
+        auto fetch_item = [&](int r, u64 (&rb)[8]) {
 #pragma unroll
-            for (int r = 0; r < 2; ++r)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int i = f_kt * UKC + 4 * ikq[r] + j;
+            for (int j = 0; j < 4; ++j) {
+                const int i = f_kt * UKC + 4 * ikq[r] + j;
 #if MFHE_UMMA_DBG & 2
-                    rb[r][2 * j] = (u64)(i + f_lrel); rb[r][2 * j + 1] = (u64)i;
+                rb[2 * j] = (u64)(i + f_lrel); rb[2 * j + 1] = (u64)i;
 #else
-                    if constexpr (SRC == kSrcMem) {
-                        const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>((const u64*)a.in + (size_t)i * istride + f_off[r]));
-                        rb[r][2 * j] = v.x; rb[r][2 * j + 1] = v.y;
-                    } else {
-                        rb[r][2 * j] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r], f_q, f_mu);
-                        rb[r][2 * j + 1] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r] + 1, f_q, f_mu);
-                    }
-#endif
+                if (!f_ok[r]) { rb[2 * j] = 0; rb[2 * j + 1] = 0; }
+                else if constexpr (SRC == kSrcMem) {
+                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>((const u64*)a.in + (size_t)i * istride + f_off[r]));
+                    rb[2 * j] = v.x; rb[2 * j + 1] = v.y;
+                } else {
+                    rb[2 * j] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r], f_q, f_mu);
+                    rb[2 * j + 1] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r] + 1, f_q, f_mu);
                 }
+#endif
+            }
+        };
+        auto f_advance = [&]() {
             f_kt += 2;
             if (f_kt >= kchunks) { f_kt = grp; ++f_it; }
         };
-        auto stash = [&](int g, const u64 (&rb)[2][8]) {
+        auto stash_item = [&](unsigned char* sB, int r, const u64 (&rb)[8]) {
+            // rows (v*UN + c), (v*UN + c + 1) of B', bytes [4kq, 4kq+4): core matrix (row/8, kq/4), row%8, (kq%4)*4.
+            // Lanes with isw set store the odd row first, so that one store instruction covers all 32 banks.
+            unsigned char* dst = sB + (ic[r] >> 3) * 512 + (ikq[r] >> 2) * 128 + (ic[r] & 7) * 16 + (ikq[r] & 3) * 4;
+            unsigned char* d1 = dst + (isw[r] ? 16 : 0);
+            unsigned char* d2 = dst + (isw[r] ? 0 : 16);
+#pragma unroll
+            for (int v = 0; v < ND; ++v) {
+                const int sh = (v < 4) ? 0 : 32;
+                const u32 sel = (u32)(v & 3) | ((u32)(4 + (v & 3)) << 4);
+                u32 wd[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const u32 x0 = (u32)(rb[0 + e] >> sh), x1 = (u32)(rb[2 + e] >> sh);
+                    const u32 x2 = (u32)(rb[4 + e] >> sh), x3 = (u32)(rb[6 + e] >> sh);
+                    wd[e] = __byte_perm(__byte_perm(x0, x1, sel), __byte_perm(x2, x3, sel), 0x5410);
+                }
+                *reinterpret_cast<u32*>(d1 + v * B_PLANE) = isw[r] ? wd[1] : wd[0];
+                *reinterpret_cast<u32*>(d2 + v * B_PLANE) = isw[r] ? wd[0] : wd[1];
+            }
+        };
+        u64 rb[R][8];
+        if (grp < my_chunks) {
+            f_tile();
+#pragma unroll
+            for (int r = 0; r < R; ++r) fetch_item(r, rb[r]);
+            f_advance();
+        }
+        for (int g = grp; g < my_chunks; g += 2) {              // kchunks is even, so is my_chunks
             const int s = g % C::NS;
+            const bool more = g + 2 < my_chunks;
             if (g >= C::NS) mbar_wait(bar_empty(s), ((g / C::NS) - 1) & 1);
             unsigned char* sB = smem + s * C::STAGE + ND * A_PLANE;
+            if (more && f_kt == grp) f_tile();                   // (only reads of the OLD f_ok / ic remain below: see order)
 #pragma unroll
-            for (int r = 0; r < 2; ++r) {
-                // rows (v*32 + c), (v*32 + c + 1) of B', bytes [4kq, 4kq+4): core matrix (row/8, kq/4), row%8, (kq%4)*4.
-                // Lanes with isw set store the odd row first, so that one store instruction covers all 32 banks.
-                unsigned char* dst = sB + (ic[r] >> 3) * 512 + (ikq[r] >> 2) * 128 + (ic[r] & 7) * 16 + (ikq[r] & 3) * 4;
-                unsigned char* d1 = dst + (isw[r] ? 16 : 0);
-                unsigned char* d2 = dst + (isw[r] ? 0 : 16);
-#pragma unroll
-                for (int v = 0; v < ND; ++v) {
-                    const int sh = (v < 4) ? 0 : 32;
-                    const u32 sel = (u32)(v & 3) | ((u32)(4 + (v & 3)) << 4);
-                    u32 wd[2];
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const u32 x0 = (u32)(rb[r][0 + e] >> sh), x1 = (u32)(rb[r][2 + e] >> sh);
-                        const u32 x2 = (u32)(rb[r][4 + e] >> sh), x3 = (u32)(rb[r][6 + e] >> sh);
-                        wd[e] = __byte_perm(__byte_perm(x0, x1, sel), __byte_perm(x2, x3, sel), 0x5410);
-                    }
-                    *reinterpret_cast<u32*>(d1 + v * B_PLANE) = isw[r] ? wd[1] : wd[0];
-                    *reinterpret_cast<u32*>(d2 + v * B_PLANE) = isw[r] ? wd[0] : wd[1];
-                }
+            for (int r = 0; r < R; ++r) {
+                if (live[r]) stash_item(sB, r, rb[r]);
+                if (more) fetch_item(r, rb[r]);
             }
+            if (more) f_advance();
 #if !(MFHE_UMMA_DBG & 8)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 #endif
             mbar_arrive(bar_fullB(s));
-        };
-        u64 rb0[2][8], rb1[2][8];
-        if (grp < my_chunks) fetch(rb0);
-        for (int g = grp; g < my_chunks; g += 4) {              // kchunks is even, so is my_chunks
-            const bool more = g + 2 < my_chunks;
-            if (more) fetch(rb1);
-            stash(g, rb0);
-            if (more) {
-                if (g + 4 < my_chunks) fetch(rb0);
-                stash(g + 2, rb1);
-            }
         }
-    } else if (warp >= 8) {
-        // ===== epilogue (8 warps): TMEM lanes 32*(warp%4).. = output rows, column half (warp-8)/4.  Sub-group sg =
+    } else {
+        // ===== epilogue (4 x UN/16 warps): TMEM lanes 32*(warp%4).. = output rows, 16-column part (warp-8)/4.  Sub-group sg =
         // (16-lane half, 8-column group): thread holds rows lane/4 and lane/4 + 8, columns 2 (lane%4) + {0, 1} =====
         const u32 tlane = tmem + ((u32)(32 * (warp & 3)) << 16);
         for (int it = 0; it < my_tiles; ++it) {
@@ -368,8 +393,10 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                 // e = 4 sg + 2 p: rows o + 16 (sg / 2) + 8 p, column pair 8 (sg % 2) + 2 (lane % 4)
                 const size_t off = poly_set_addr(a.out_layout, o + 16 * (e >> 3) + 8 * ((e >> 1) & 1), lrel,
                                                  ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3), a.n, a.cols, a.limbs);
-                *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[0], r[1]);
-                if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[0], r[1]);
+                if (ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3) < a.cols) {      // ragged last column block
+                    *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[0], r[1]);
+                    if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[0], r[1]);
+                }
             }
         }
     }
@@ -391,8 +418,8 @@ static cudaError_t launch_umma_nd(const WcrtArgs& a, cudaStream_t st) {
     }
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-    const int ntiles = (a.cols / UN) * (a.phi / UM) * a.lzn;
-    wcrt_umma_kernel<SRC, ND><<<ntiles < sms ? ntiles : sms, UTHREADS, C::SMEM, st>>>(a, ntiles);
+    const int ntiles = ((a.cols + C::UN - 1) / C::UN) * (a.phi / UM) * a.lzn;
+    wcrt_umma_kernel<SRC, ND><<<ntiles < sms ? ntiles : sms, C::THREADS, C::SMEM, st>>>(a, ntiles);
     return cudaGetLastError();
 }
 
@@ -407,7 +434,7 @@ static cudaError_t launch_umma_src(const WcrtArgs& a, int nd, cudaStream_t st) {
 }
 
 bool wcrt_umma_eligible(const WcrtArgs& a) {
-    return a.tabt && a.h_ndig && a.phi % UM == 0 && a.phi % (2 * UKC) == 0 && a.cols % UN == 0 && a.n % 2 == 0;
+    return a.tabt && a.h_ndig && a.phi % UM == 0 && a.phi % (2 * UKC) == 0 && a.cols % 16 == 0 && a.n % 2 == 0;
 }
 
 cudaError_t wcrt_umma_launch(const WcrtArgs& a, int nd, cudaStream_t st) {
