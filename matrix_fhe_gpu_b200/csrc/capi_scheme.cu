@@ -374,15 +374,16 @@ extern "C" int mfhe_encode(mfhe_ctx* c, const double* msg, uint64_t* out_re, uin
     cudaError_t e = xy_sandwich_launch(c->d_xyVinv, c->d_xyVinvT, (const double2*)msg, xy, c->n, c->phi, st);
     if (e == cudaSuccess) e = wdft_launch(wdft_tab(c, true), xy, wc, c->phi, (int)c->n2(), st);
     // 3) llround(z * delta) once per value into two int64 planes (they reuse the xy buffer, dead by now)
-    // 4) W-CRT with the signed-integer loader (value mod q_l per limb), matrix-major result written directly
+    // 4) W-CRT: per-limb residues of a plane written to scratch, then the tensor-core GEMM, matrix-major result
     const size_t total = (size_t)c->phi * c->n2();
     long long* qre = (long long*)xy;
     long long* qim = qre + total;
+    u64* scratch = (u64*)c->take(c->T() * 8);           // optional: without it the loader reduces on the fly
     if (e == cudaSuccess) e = llround_planes_launch(wc, qre, qim, total, c->delta, st);
     for (int part = 0; part < 2 && e == cudaSuccess; ++part) {
         WcrtArgs a = wcrt_args(c, false);
         a.in = part ? qim : qre; a.out = (u64*)(part ? out_im : out_re);
-        a.source = kSrcI64; a.out_layout = MFHE_LAYOUT_MATRIX;
+        a.source = kSrcI64; a.out_layout = MFHE_LAYOUT_MATRIX; a.scratch = scratch;
         e = wcrt_launch(a, st);
     }
     return done(e, "encode");
@@ -474,6 +475,9 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
     // a: W-coeff -> W-eval, written straight into the ciphertexts' a halves (matrix-major)
     WcrtArgs a = wcrt_args(c, false);
     a.source = a_src; a.in = a_coeff; a.out = (u64*)ct_re + T; a.out2 = ct_im ? (u64*)ct_im + T : nullptr;
+    // scratch for a sampled `a`: the b half of ct_re is free until the row kernel writes it (unless the caller
+    // encrypts in place), else the arena
+    a.scratch = ((const void*)m_re != (const void*)ct_re && (const void*)m_im != (const void*)ct_re) ? (u64*)ct_re : (u64*)c->take(T * 8);
     cudaError_t e = wcrt_launch(a, st);
     // e: W-coeff -> W-eval (the reference draws the same gaussian stream for e_re and e_im: HE.cu:1516-1517)
     if (e == cudaSuccess) {
@@ -484,6 +488,7 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
             if (!tab) return fail(MFHE_ENOMEM, std::string(who) + ": arena too small");
             e = gauss_table_launch(tab, c->phi, (int)c->n2(), st);
             g.in = tab;
+            g.scratch = (u64*)c->take(T * 8);   // optional
         }
         if (e == cudaSuccess) e = wcrt_launch(g, st);
         if (e == cudaSuccess && two_e) { g.in = e_im; g.out = E1; e = wcrt_launch(g, st); }

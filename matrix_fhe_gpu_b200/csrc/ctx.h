@@ -75,6 +75,10 @@ struct WcrtArgs {
     const unsigned char* tabt = nullptr;   // digit tables pre-tiled for UMMA (tcgen05 path), may be null
     const int* h_ndig = nullptr;           // HOST array [limbs]: 8-bit digits per modulus
     int lz0 = 0, lzn = 0;                  // relative limb window of one launch (set by wcrt_launch)
+    // optional [phi][limbs][cols] words: on the tcgen05 path a computing source (int64, quantiser, samplers) is first
+    // written out as canonical residues here and the GEMM then runs on the plain-memory loader (the fused loaders
+    // cannot feed 128 x 48 tiles fast enough; the extra pass is 2 x S of HBM traffic, ~0.06 ms at L = 11)
+    u64* scratch = nullptr;
 };
 cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st);
 // kSrcGauss input: int8 noise value of every logical coefficient [phi][cols]

@@ -203,6 +203,34 @@ cudaError_t wcrt_umma_launch(const WcrtArgs& a, int nd, cudaStream_t st);
 // digits): the tcgen05 / TMEM kernel (wcrt_umma.cu) when the shape divides its 128 x 32 x 64 tiling, else the
 // mma.sync kernel (wcrt_tc.cu); wider moduli and other shapes go to the CUDA-core kernel above.
 // MFHE_WCRT_PATH = umma | mma | cuda in the environment pins the choice (A/B measurements, parity tests).
+// out[i][lrel][c] = canonical residue the fused loader of `SRC` would produce (two columns per thread)
+template <int SRC>
+__global__ void __launch_bounds__(256)
+wcrt_materialize_kernel(const WcrtArgs a, u64* __restrict__ out, size_t total2) {
+    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i2 >= total2) return;
+    const size_t idx = i2 * 2;
+    const int c = (int)(idx % a.cols);
+    const size_t t = idx / a.cols;
+    const int lrel = (int)(t % a.limbs), i = (int)(t / a.limbs), l = a.limb0 + lrel;
+    const u64 q = a.moduli[l], mu_hi = a.mu[l].y;
+    const u64 v0 = wcrt_load_one<SRC>(a, i, l, c, q, mu_hi), v1 = wcrt_load_one<SRC>(a, i, l, c + 1, q, mu_hi);
+    *reinterpret_cast<ulonglong2*>(out + idx) = make_ulonglong2(v0, v1);
+}
+static cudaError_t wcrt_materialize(const WcrtArgs& a, cudaStream_t st) {
+    const size_t total2 = (size_t)a.phi * a.limbs * a.cols / 2;
+    const unsigned grid = (unsigned)((total2 + 255) / 256);
+    switch (a.source) {
+        case kSrcI64:     wcrt_materialize_kernel<kSrcI64><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        case kSrcQuantRe: wcrt_materialize_kernel<kSrcQuantRe><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        case kSrcQuantIm: wcrt_materialize_kernel<kSrcQuantIm><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        case kSrcUniform: wcrt_materialize_kernel<kSrcUniform><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        case kSrcGauss:   wcrt_materialize_kernel<kSrcGauss><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t wcrt_launch(const WcrtArgs& a0, cudaStream_t st) {
     if (a0.cols % 4 || a0.phi % 4 || a0.n % 4) return cudaErrorInvalidValue;
     const int pin = [] {
@@ -213,6 +241,11 @@ cudaError_t wcrt_launch(const WcrtArgs& a0, cudaStream_t st) {
     WcrtArgs a = a0;
     const bool umma = (pin == 0 || pin == 1) && wcrt_umma_eligible(a);
     const bool mma = !umma && pin != 3 && wcrt_tc_eligible(a);
+    if (umma && a.source != kSrcMem && a.scratch && a.cols % 2 == 0) {
+        cudaError_t em = wcrt_materialize(a, st);
+        if (em != cudaSuccess) return em;
+        a.in = a.scratch; a.source = kSrcMem; a.in_layout = MFHE_LAYOUT_MATRIX;
+    }
     auto digits = [&](int lrel) { const int nd = (umma || mma) ? a.h_ndig[a.limb0 + lrel] : 99; return nd <= 4 ? 4 : nd; };
     cudaError_t e = cudaSuccess;
     for (int z = 0; z < a0.limbs && e == cudaSuccess;) {

@@ -96,7 +96,7 @@ __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
 }
 }  // namespace
 
-template <int ND> struct UmmaCfg {
+template <int ND, int SRC> struct UmmaCfg {
     // Tile width.  A 128-row kind::i8 instruction costs ~130-160 clk whatever its N (profiles/r1_10_wcrt_limiters.txt,
     // third series), so the instruction is made as wide as TMEM allows: N' = ND * UN <= 256, (2ND-1) * UN <= 512.
     static constexpr int UN = (ND >= 6) ? 32 : 48;
@@ -105,7 +105,10 @@ template <int ND> struct UmmaCfg {
     static constexpr int PROD_ROUNDS = (2 * NCG + 3) / 4;               // producer items per thread and chunk
     static constexpr int EPI_PARTS = UN / 16;                           // epilogue: 16 columns per warp
     static constexpr int EPI_WARPS = 4 * EPI_PARTS;
-    static constexpr int ISSUE_WARP = 8 + EPI_WARPS;
+    // producer groups of 4 warps, each taking every PG-th chunk: plain memory input keeps up with one group (17 warps,
+    // 96 registers, no spills); the computing sources (int64 reduction, samplers) need two (21 warps, 80 registers)
+    static constexpr int PG = (SRC == kSrcMem) ? 1 : 2, PROD_WARPS = 4 * PG;
+    static constexpr int ISSUE_WARP = PROD_WARPS + EPI_WARPS;
     static constexpr int THREADS = (ISSUE_WARP + 1) * 32;
     static constexpr int NS = (ND <= 5) ? 4 : 3;                       // ring stages
     static constexpr int STAGE = ND * (A_PLANE + B_PLANE);
@@ -124,9 +127,9 @@ __device__ __forceinline__ TileIdx tile_decode(int tile, int nOT, int nCB) {
 }
 
 template <int SRC, int ND>
-__global__ void __launch_bounds__(UmmaCfg<ND>::THREADS, 1)
+__global__ void __launch_bounds__(UmmaCfg<ND, SRC>::THREADS, 1)
 wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
-    using C = UmmaCfg<ND>;
+    using C = UmmaCfg<ND, SRC>;
     constexpr int UN = C::UN, B_PLANE = C::B_PLANE;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
@@ -222,7 +225,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             }
         }
         __syncwarp();
-    } else if (warp < 8) {
+    } else if (warp < C::PROD_WARPS) {
         // ===== input-digit producers: two groups of 128 threads take alternate chunks.  A chunk of one digit stack is
         // NCG column groups x 2 halves of the 16 four-k groups = 2 NCG warp-items; a lane of a warp-item owns (column
         // pair, four consecutive i): 4 LDG.128, PRMT byte transposes, K-major core-matrix stores.  One register set
@@ -278,7 +281,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             }
         };
         auto f_advance = [&]() {
-            f_kt += 2;
+            f_kt += C::PG;
             if (f_kt >= kchunks) { f_kt = grp; ++f_it; }
         };
         auto stash_item = [&](unsigned char* sB, int r, const u64 (&rb)[8]) {
@@ -309,9 +312,9 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             for (int r = 0; r < R; ++r) fetch_item(r, rb[r]);
             f_advance();
         }
-        for (int g = grp; g < my_chunks; g += 2) {              // kchunks is even, so is my_chunks
+        for (int g = grp; g < my_chunks; g += C::PG) {           // kchunks is even, so is my_chunks
             const int s = g % C::NS;
-            const bool more = g + 2 < my_chunks;
+            const bool more = g + C::PG < my_chunks;
             if (g >= C::NS) mbar_wait(bar_empty(s), ((g / C::NS) - 1) & 1);
             unsigned char* sB = smem + s * C::STAGE + ND * A_PLANE;
             if (more && f_kt == grp) f_tile();                   // (only reads of the OLD f_ok / ic remain below: see order)
@@ -341,7 +344,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             // phase 1 (holds TMEM): fold the 2ND-1 partial sums of each of this thread's 16 outputs into
             //   lo = sum_{w<5} S_w 2^(8w)  (< 2^61)   and   up = sum_{5<=w<10} S_w 2^(8(w-5))  (< 2^61)   [+ S_10 for ND = 6],
             // 4 columns at a time to keep the register footprint small
-            const int ccol = ((warp - 8) >> 2) * 16;
+            const int ccol = ((warp - C::PROD_WARPS) >> 2) * 16;
             u64 vlo[16], vup[16];
             u32 vtop[(2 * ND - 1 > 10) ? 16 : 1];         // position 10 (scale 2^80) exists for ND = 6 only
 #pragma unroll
@@ -409,7 +412,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
 
 template <int SRC, int ND>
 static cudaError_t launch_umma_nd(const WcrtArgs& a, cudaStream_t st) {
-    using C = UmmaCfg<ND>;
+    using C = UmmaCfg<ND, SRC>;
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(wcrt_umma_kernel<SRC, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
