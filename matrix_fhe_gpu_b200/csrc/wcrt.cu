@@ -203,29 +203,27 @@ cudaError_t wcrt_umma_launch(const WcrtArgs& a, int nd, cudaStream_t st);
 // digits): the tcgen05 / TMEM kernel (wcrt_umma.cu) when the shape divides its 128 x 32 x 64 tiling, else the
 // mma.sync kernel (wcrt_tc.cu); wider moduli and other shapes go to the CUDA-core kernel above.
 // MFHE_WCRT_PATH = umma | mma | cuda in the environment pins the choice (A/B measurements, parity tests).
-// out[i][lrel][c] = canonical residue the fused loader of `SRC` would produce (two columns per thread)
+// out[i][lrel][c] = canonical residue the fused loader of `SRC` would produce.  grid = (column pairs / 256, limbs, phi):
+// no index divisions, two columns (16 bytes) per thread, coalesced along c
 template <int SRC>
 __global__ void __launch_bounds__(256)
-wcrt_materialize_kernel(const WcrtArgs a, u64* __restrict__ out, size_t total2) {
-    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i2 >= total2) return;
-    const size_t idx = i2 * 2;
-    const int c = (int)(idx % a.cols);
-    const size_t t = idx / a.cols;
-    const int lrel = (int)(t % a.limbs), i = (int)(t / a.limbs), l = a.limb0 + lrel;
+wcrt_materialize_kernel(const WcrtArgs a, u64* __restrict__ out) {
+    const int c = 2 * (int)(blockIdx.x * 256 + threadIdx.x);
+    if (c >= a.cols) return;
+    const int lrel = blockIdx.y, i = blockIdx.z, l = a.limb0 + lrel;
     const u64 q = a.moduli[l], mu_hi = a.mu[l].y;
     const u64 v0 = wcrt_load_one<SRC>(a, i, l, c, q, mu_hi), v1 = wcrt_load_one<SRC>(a, i, l, c + 1, q, mu_hi);
-    *reinterpret_cast<ulonglong2*>(out + idx) = make_ulonglong2(v0, v1);
+    *reinterpret_cast<ulonglong2*>(out + ((size_t)i * a.limbs + lrel) * a.cols + c) = make_ulonglong2(v0, v1);
 }
 static cudaError_t wcrt_materialize(const WcrtArgs& a, cudaStream_t st) {
-    const size_t total2 = (size_t)a.phi * a.limbs * a.cols / 2;
-    const unsigned grid = (unsigned)((total2 + 255) / 256);
+    if (a.limbs > 65535 || a.phi > 65535) return cudaErrorInvalidValue;
+    const dim3 grid((unsigned)((a.cols / 2 + 255) / 256), (unsigned)a.limbs, (unsigned)a.phi);
     switch (a.source) {
-        case kSrcI64:     wcrt_materialize_kernel<kSrcI64><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
-        case kSrcQuantRe: wcrt_materialize_kernel<kSrcQuantRe><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
-        case kSrcQuantIm: wcrt_materialize_kernel<kSrcQuantIm><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
-        case kSrcUniform: wcrt_materialize_kernel<kSrcUniform><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
-        case kSrcGauss:   wcrt_materialize_kernel<kSrcGauss><<<grid, 256, 0, st>>>(a, a.scratch, total2); break;
+        case kSrcI64:     wcrt_materialize_kernel<kSrcI64><<<grid, 256, 0, st>>>(a, a.scratch); break;
+        case kSrcQuantRe: wcrt_materialize_kernel<kSrcQuantRe><<<grid, 256, 0, st>>>(a, a.scratch); break;
+        case kSrcQuantIm: wcrt_materialize_kernel<kSrcQuantIm><<<grid, 256, 0, st>>>(a, a.scratch); break;
+        case kSrcUniform: wcrt_materialize_kernel<kSrcUniform><<<grid, 256, 0, st>>>(a, a.scratch); break;
+        case kSrcGauss:   wcrt_materialize_kernel<kSrcGauss><<<grid, 256, 0, st>>>(a, a.scratch); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

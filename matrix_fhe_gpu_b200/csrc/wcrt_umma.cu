@@ -99,11 +99,11 @@ __device__ __forceinline__ void tmem_st8_zero(u32 taddr) {
 template <int ND, int SRC> struct UmmaCfg {
     // Tile width.  A 128-row kind::i8 instruction costs ~130-160 clk whatever its N (profiles/r1_10_wcrt_limiters.txt,
     // third series), so the instruction is made as wide as TMEM allows: N' = ND * UN <= 256, (2ND-1) * UN <= 512.
-    static constexpr int UN = (ND >= 6) ? 32 : 48;
+    static constexpr int UN = (ND >= 6) ? 40 : 48;
     static constexpr int B_PLANE = UN * UKC;                            // one input digit plane of one chunk
     static constexpr int NCG = UN / 8;                                  // 8-column groups
     static constexpr int PROD_ROUNDS = (2 * NCG + 3) / 4;               // producer items per thread and chunk
-    static constexpr int EPI_PARTS = UN / 16;                           // epilogue: 16 columns per warp
+    static constexpr int EPI_PARTS = (UN + 15) / 16;                    // epilogue: 16 columns per warp (the last part may hold 8)
     static constexpr int EPI_WARPS = 4 * EPI_PARTS;
     // producer groups of 4 warps, each taking every PG-th chunk: plain memory input keeps up with one group (17 warps,
     // 96 registers, no spills); the computing sources (int64 reduction, samplers) need two (21 warps, 80 registers)
@@ -112,9 +112,13 @@ template <int ND, int SRC> struct UmmaCfg {
     static constexpr int THREADS = (ISSUE_WARP + 1) * 32;
     static constexpr int NS = (ND <= 5) ? 4 : 3;                       // ring stages
     static constexpr int STAGE = ND * (A_PLANE + B_PLANE);
-    static constexpr int SMEM = NS * STAGE + 1024;                      // + barriers / TMEM pointer, alignment slack
+    // first K step of a tile: if the accumulate / overwrite pieces would not be multiples of 16 columns (ND = 6,
+    // UN = 40) the upper positions are instead cleared by one extra instruction with an all-zero A tile
+    static constexpr bool ZERO_FIRST = ((ND - 1) * UN) % 16 != 0;
+    static constexpr int ZPAD = ZERO_FIRST ? A_PLANE : 0;
+    static constexpr int SMEM = NS * STAGE + ZPAD + 1024;               // + barriers / TMEM pointer, alignment slack
     static constexpr int ACC_COLS = (2 * ND - 1) * UN;
-    static_assert(ACC_COLS <= 512 && ND * UN <= 256 && (ND * UN) % 16 == 0 && UN % 16 == 0, "tile width");
+    static_assert(ACC_COLS <= 512 && ND * UN <= 256 && (ND * UN) % 16 == 0 && UN % 8 == 0, "tile width");
     // kind::i8 instruction descriptor: D = s32, A = B = unsigned 8 bit, both K-major, 128 x N
     __host__ __device__ static constexpr u32 idesc(int n) { return (2u << 4) | ((u32)(n >> 3) << 17) | ((u32)(UM >> 4) << 24); }
 };
@@ -133,7 +137,8 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     constexpr int UN = C::UN, B_PLANE = C::B_PLANE;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
-    unsigned char* ctrl = smem + C::NS * C::STAGE;        // barriers: fullA[NS], fullB[NS], empty[NS], tmem_full, tmem_empty
+    unsigned char* zpad = smem + C::NS * C::STAGE;        // all-zero A tile (ZERO_FIRST only)
+    unsigned char* ctrl = zpad + C::ZPAD;                 // barriers: fullA[NS], fullB[NS], empty[NS], tmem_full, tmem_empty
     const u32 bar0 = smem_u32(ctrl);
     auto bar_fullA = [&](int s) { return bar0 + 8u * s; };
     auto bar_fullB = [&](int s) { return bar0 + 8u * (C::NS + s); };
@@ -150,6 +155,10 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
         for (int s = 0; s < C::NS; ++s) { mbar_init(bar_fullA(s), 1); mbar_init(bar_fullB(s), 128); mbar_init(bar_empty(s), 1); }
         mbar_init(bar_tfull, 1); mbar_init(bar_tempty, C::EPI_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if constexpr (C::ZERO_FIRST) {
+        for (int i = t; i < C::ZPAD / 16; i += C::THREADS) reinterpret_cast<uint4*>(zpad)[i] = make_uint4(0, 0, 0, 0);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     if (warp == 0) {
         __syncwarp();
@@ -193,6 +202,13 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                     if (kt == 0 && ks == 0) {
                         // first K step of a tile: nothing to accumulate onto.  Position block u+ND-1 is new for
                         // every u, the others were started by u-1: split the instruction accordingly.
+                        if constexpr (C::ZERO_FIRST) {
+                            umma_i8(tmem + (u32)((ND - 1) * UN), umma_desc(smem_u32(zpad), 128, 512), bdesc, C::idesc(ND * UN), 0);
+                            umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, C::idesc(ND * UN), 0);
+#pragma unroll
+                            for (int u = 1; u < ND; ++u)
+                                umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE, 128, 512), bdesc, C::idesc(ND * UN), 1);
+                        } else {
                         umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, C::idesc(ND * UN), 0);
 #pragma unroll
                         for (int u = 1; u < ND; ++u) {
@@ -200,6 +216,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                             umma_i8(tmem + (u32)(u * UN), adesc, bdesc, C::idesc((ND - 1) * UN), 1);
                             umma_i8(tmem + (u32)((u + ND - 1) * UN), adesc, umma_desc(sb + (ND - 1) * B_PLANE, 128, 512),
                                     C::idesc(UN), 0);
+                        }
                         }
                     } else {
 #ifdef MFHE_UMMA_DBGN      // operand-fetch experiment: every instruction with N = MFHE_UMMA_DBGN (results are garbage)
@@ -349,6 +366,7 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             u32 vtop[(2 * ND - 1 > 10) ? 16 : 1];         // position 10 (scale 2^80) exists for ND = 6 only
 #pragma unroll
             for (int sg = 0; sg < 4; ++sg) {
+                if (ccol + 8 * (sg & 1) >= UN) continue;          // last part of a tile whose width is not a multiple of 16
                 u32 acc[2 * ND - 1][4];
 #pragma unroll
                 for (int w = 0; w < 2 * ND - 1; ++w)
@@ -396,7 +414,8 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                 // e = 4 sg + 2 p: rows o + 16 (sg / 2) + 8 p, column pair 8 (sg % 2) + 2 (lane % 4)
                 const size_t off = poly_set_addr(a.out_layout, o + 16 * (e >> 3) + 8 * ((e >> 1) & 1), lrel,
                                                  ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3), a.n, a.cols, a.limbs);
-                if (ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3) < a.cols) {      // ragged last column block
+                if (ccol + 8 * ((e >> 2) & 1) < UN &&
+                    ti.cblk * UN + ccol + 8 * ((e >> 2) & 1) + 2 * (lane & 3) < a.cols) {      // ragged last column block
                     *reinterpret_cast<ulonglong2*>(a.out + off) = make_ulonglong2(r[0], r[1]);
                     if (a.out2) *reinterpret_cast<ulonglong2*>(a.out2 + off) = make_ulonglong2(r[0], r[1]);
                 }
