@@ -101,7 +101,7 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2):
                                        "roofline": {"bound": "tensor", "achieved": 2e-12 * macs8 / (ms_w * 1e-3),
                                                     "peak": 2e-12 * peak8, "unit": "Top/s (int8)",
                                                     "frac": macs8 / (ms_w * 1e-3) / peak8, "peak_source": src},
-                                       "kernel": "wcrt_umma_kernel (tcgen05.mma kind::i8), profiles/r1_07_ncu_umma_summary.txt"}
+                                       "kernel": "wcrt_umma_kernel (tcgen05.mma kind::i8), profiles/r1_12_ncu_umma_summary.txt"}
             del a_u
             zero = torch.zeros_like(sk)
             ct_r, ct_i = g.allocate_ciphertext(), g.allocate_ciphertext()
