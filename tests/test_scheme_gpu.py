@@ -20,6 +20,10 @@ SHAPES = {
     "tiny": (16, 5, lambda: O.primes_congruent_one(960, 35, 3), 2.0 ** 30),
     "mid": (16, 17, lambda: O.primes_congruent_one(64 * 51, 45, 1) + O.primes_congruent_one(64 * 51, 35, 3), 2.0 ** 30),
     "wide": (32, 5, lambda: O.primes_congruent_one(128 * 15, 55, 2) + O.primes_congruent_one(128 * 15, 40, 1), 2.0 ** 35),
+    # the reference's p = 771 (phi = 512) and its first three moduli (45, 35, 35 bits) at n = 16: the smallest shape the
+    # tcgen05 W-CRT takes (both digit counts, ragged last column block: 256 = 5*48 + 16 = 6*40 + 16), so every test
+    # below also checks that kernel against the full oracle
+    "p771": (16, 257, lambda: [17592186435073, 17182765057, 17184541441], 2.0 ** 35),
 }
 
 
