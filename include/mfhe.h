@@ -93,6 +93,16 @@ int mfhe_poly_add(const mfhe_ntt_plan *plan, const uint64_t *d_a, const uint64_t
 int mfhe_poly_sub(const mfhe_ntt_plan *plan, const uint64_t *d_a, const uint64_t *d_b,
                   uint64_t *d_out, size_t batch, void *stream);
 
+/* Ring product of every limb-poly of a with that of b:  a <- INTT(NTT(a) (.) NTT(b))  (X^N + 1 for the Phantom
+ * convention; the plan's ring otherwise), canonical residues in and out, coefficient order in and out.
+ * b is transformed in place and LEFT in NTT form (pass b_is_ntt != 0 if it already is: one operand reused for
+ * many products).  For N >= 2^12 the pointwise product is applied while the first inverse pass loads its data,
+ * so there is no pass of its own over a and b.  Replaces the sequence nwt_2d_radix8_forward_inplace x2 /
+ * multiply_rns_poly / nwt_2d_radix8_backward_inplace (ph/src/ntt/fntt_2d.cu:620-653, intt_2d.cu:724-757) and, for
+ * n <= 256, the reference's NTT_X / pointwise_mul / INTT_X chains (src/core/HE.cu:1508-1530). */
+int mfhe_ntt_mul_intt(const mfhe_ntt_plan *plan, uint64_t *d_a, uint64_t *d_b, int b_is_ntt,
+                      size_t batch, void *stream);
+
 
 /* ======================================================================== *
  * Matrix pipeline (family B of SURVEY.md): the reference's native ring

@@ -63,6 +63,8 @@ def lib() -> C.CDLL:
         for name in ("mfhe_poly_mul", "mfhe_poly_add", "mfhe_poly_sub"):
             getattr(L, name).restype = C.c_int
             getattr(L, name).argtypes = [_vp, _vp, _vp, _vp, C.c_size_t, _vp]
+        L.mfhe_ntt_mul_intt.restype = C.c_int
+        L.mfhe_ntt_mul_intt.argtypes = [_vp, _vp, _vp, C.c_int, C.c_size_t, _vp]
         _lib = L
     return _lib
 
@@ -167,6 +169,12 @@ class NttPlan:
 
     def mul(self, a, b, out=None, stream=None):
         return self._pw(lib().mfhe_poly_mul, a, b, out, stream)
+
+    def mul_intt_(self, a, b, b_is_ntt=False, stream=None):
+        """a <- INTT(NTT(a) . NTT(b)) in place; b is left in NTT form (mfhe_ntt_mul_intt)."""
+        check(lib().mfhe_ntt_mul_intt(self._h, _dev_ptr(a), _dev_ptr(b), int(bool(b_is_ntt)), self._batch(a),
+                                      _stream_handle(stream)))
+        return a
 
     def add(self, a, b, out=None, stream=None):
         return self._pw(lib().mfhe_poly_add, a, b, out, stream)

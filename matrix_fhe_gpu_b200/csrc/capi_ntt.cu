@@ -223,3 +223,19 @@ static int pointwise(const mfhe_ntt_plan* p, int op, const uint64_t* a, const ui
 extern "C" int mfhe_poly_mul(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kMul, a, b, o, batch, s); }
 extern "C" int mfhe_poly_add(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kAdd, a, b, o, batch, s); }
 extern "C" int mfhe_poly_sub(const mfhe_ntt_plan* p, const uint64_t* a, const uint64_t* b, uint64_t* o, size_t batch, void* s) { return pointwise(p, kSub, a, b, o, batch, s); }
+
+// a <- INTT(NTT(a) (.) NTT(b)); b ends up in NTT form.  Flat plans multiply inside the first inverse pass.
+extern "C" int mfhe_ntt_mul_intt(const mfhe_ntt_plan* p, uint64_t* a, uint64_t* b, int b_is_ntt, size_t batch, void* s) {
+    if (!p || ((!a || !b) && batch)) return fail(MFHE_EINVAL, "ntt_mul_intt: NULL plan or data");
+    if (a == b) return fail(MFHE_EINVAL, "ntt_mul_intt: a and b must be different buffers");
+    if (batch == 0) return MFHE_OK;
+    int rc = run(p, true, a, batch, 0, p->L, s);
+    if (rc == MFHE_OK && !b_is_ntt) rc = run(p, true, b, batch, 0, p->L, s);
+    if (rc != MFHE_OK) return rc;
+    if (p->logn <= 8) {
+        rc = pointwise(p, kMul, a, b, a, batch, s);
+        return rc == MFHE_OK ? run(p, false, a, batch, 0, p->L, s) : rc;
+    }
+    cudaError_t e = ntt_flat_launch(false, (u64*)a, p->flat(), 0, p->L, batch, p->chunk, (cudaStream_t)s, (const u64*)b, p->d_mu);
+    return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "ntt_mul_intt");
+}

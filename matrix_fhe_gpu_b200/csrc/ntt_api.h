@@ -7,9 +7,10 @@
 namespace mfhe {
 
 // flat negacyclic NTT, N = 2^12..2^17 (ntt_flat.cu)
+// inverse only: `mul` (same shape as data, NTT form) is multiplied in while the first pass loads, mu = floor(2^128/q)
 cudaError_t ntt_flat_launch(bool forward, u64* data, const NttTables& T, int limb_start,
                             int limb_count, size_t batch, size_t chunk_limb_polys,
-                            cudaStream_t st);
+                            cudaStream_t st, const u64* mul = nullptr, const ulonglong2* mu = nullptr);
 
 // small transforms, n = 2^3..2^8, one warp-slice per limb-poly (ntt_small.cu)
 enum SmallConvention { kPhantomNegacyclic = 0, kGlXnMinusI = 1, kCyclicNatural = 2 };

@@ -179,9 +179,12 @@ ntt_rows_fwd_kernel(u64* __restrict__ data, NttTables T, int limb_start, int lim
     }
 }
 
-template <int LOGN, int PB>
+// MUL: the pointwise product with `mul` (same layout, NTT form, canonical) is applied to the loaded values, so that
+// NTT . pointwise . INTT needs no pass of its own for the product (mfhe_ntt_mul_intt)
+template <int LOGN, int PB, bool MUL>
 __global__ void __launch_bounds__(kRowWarps * 32, MFHE_ROW_MINB)
-ntt_rows_inv_kernel(u64* __restrict__ data, NttTables T, int limb_start, int limb_count) {
+ntt_rows_inv_kernel(u64* __restrict__ data, NttTables T, int limb_start, int limb_count,
+                    const u64* __restrict__ mul, const ulonglong2* __restrict__ mu) {
     __shared__ __align__(16) u64 sm_all[kRowWarps * PB * 256];
     const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     u64* sm = sm_all + warp * (PB * 256);
@@ -202,6 +205,19 @@ ntt_rows_inv_kernel(u64* __restrict__ data, NttTables T, int limb_start, int lim
     for (int p = 0; p < PB; ++p) {
         ld256(g + p * pstride + (lane << 3), v[p][0], v[p][1], v[p][2], v[p][3]);
         ld256(g + p * pstride + (lane << 3) + 4, v[p][4], v[p][5], v[p][6], v[p][7]);
+    }
+    if constexpr (MUL) {
+        const ulonglong2 m = mu[limb];
+        const barrett1_t bc = make_barrett1(qc.q, m.x, m.y);
+        const u64* gm = mul + (g - data);
+#pragma unroll
+        for (int p = 0; p < PB; ++p) {
+            u64 b[8];
+            ld256(gm + p * pstride + (lane << 3), b[0], b[1], b[2], b[3]);
+            ld256(gm + p * pstride + (lane << 3) + 4, b[4], b[5], b[6], b[7]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[p][j] = mul_barrett1(v[p][j], b[j], bc);
+        }
     }
     inv_pass<LOGN, 0, 7, PB>(v, gbase | (lane << 3), itw, qc, ninv, w1n);
 #pragma unroll
@@ -245,7 +261,7 @@ ntt_rows_inv_kernel(u64* __restrict__ data, NttTables T, int limb_start, int lim
 // ---------------------------------------------------------------------------
 template <int LOGN, int PB>
 static cudaError_t launch_pair(bool fwd, u64* data, const NttTables& T, int limb_start, int limb_count,
-                               size_t polys, cudaStream_t st) {
+                               size_t polys, cudaStream_t st, const u64* mul, const ulonglong2* mu) {
     constexpr int LOGR = LOGN - 8;
     constexpr size_t col_smem = (size_t)PB * 4096 * sizeof(u64);
     static bool attr_done = false;
@@ -261,7 +277,8 @@ static cudaError_t launch_pair(bool fwd, u64* data, const NttTables& T, int limb
         ntt_cols_kernel<LOGN, true, PB><<<gc, kColThreads, col_smem, st>>>(data, T, limb_start, limb_count);
         ntt_rows_fwd_kernel<LOGN, PB><<<gr, kRowWarps * 32, 0, st>>>(data, T, limb_start, limb_count);
     } else {
-        ntt_rows_inv_kernel<LOGN, PB><<<gr, kRowWarps * 32, 0, st>>>(data, T, limb_start, limb_count);
+        if (mul) ntt_rows_inv_kernel<LOGN, PB, true><<<gr, kRowWarps * 32, 0, st>>>(data, T, limb_start, limb_count, mul, mu);
+        else     ntt_rows_inv_kernel<LOGN, PB, false><<<gr, kRowWarps * 32, 0, st>>>(data, T, limb_start, limb_count, nullptr, nullptr);
         ntt_cols_kernel<LOGN, false, PB><<<gc, kColThreads, col_smem, st>>>(data, T, limb_start, limb_count);
     }
     return cudaGetLastError();
@@ -271,14 +288,15 @@ constexpr int kPB = MFHE_PB;       // polys per thread group (twiddle reuse fact
 
 template <int LOGN>
 static cudaError_t launch_polys(bool fwd, u64* data, const NttTables& T, int limb_start, int limb_count,
-                                size_t polys, cudaStream_t st) {
+                                size_t polys, cudaStream_t st, const u64* mul, const ulonglong2* mu) {
     // whole PB-groups first, then the remainder one poly at a time
     const size_t main = polys - polys % kPB;
     cudaError_t err = cudaSuccess;
-    if (main) err = launch_pair<LOGN, kPB>(fwd, data, T, limb_start, limb_count, main, st);
-    if (err == cudaSuccess && polys > main)
-        err = launch_pair<LOGN, 1>(fwd, data + ((main * (size_t)limb_count) << LOGN), T, limb_start, limb_count,
-                                   polys - main, st);
+    if (main) err = launch_pair<LOGN, kPB>(fwd, data, T, limb_start, limb_count, main, st, mul, mu);
+    if (err == cudaSuccess && polys > main) {
+        const size_t off = (main * (size_t)limb_count) << LOGN;
+        err = launch_pair<LOGN, 1>(fwd, data + off, T, limb_start, limb_count, polys - main, st, mul ? mul + off : nullptr, mu);
+    }
     return err;
 }
 
@@ -286,7 +304,9 @@ static cudaError_t launch_polys(bool fwd, u64* data, const NttTables& T, int lim
 // (optionally, chunk_limb_polys != 0) so that a chunk's footprint stays L2-resident between the
 // column and the row kernel.
 cudaError_t ntt_flat_launch(bool forward, u64* data, const NttTables& T, int limb_start,
-                            int limb_count, size_t batch, size_t chunk_limb_polys, cudaStream_t st) {
+                            int limb_count, size_t batch, size_t chunk_limb_polys, cudaStream_t st,
+                            const u64* mul, const ulonglong2* mu) {
+    if (mul && (forward || !mu)) return cudaErrorInvalidValue;
     if (limb_count <= 0) return cudaErrorInvalidValue;
     size_t chunk = chunk_limb_polys ? chunk_limb_polys / (size_t)limb_count : batch;
     if (chunk == 0) chunk = 1;
@@ -297,8 +317,10 @@ cudaError_t ntt_flat_launch(bool forward, u64* data, const NttTables& T, int lim
     cudaError_t err = cudaSuccess;
     for (size_t off = 0; off < batch && err == cudaSuccess; off += chunk) {
         const size_t cnt = (batch - off < chunk) ? batch - off : chunk;
-        u64* p = data + ((off * (size_t)limb_count) << T.logn);
-#define MFHE_CASE(LN) case LN: err = launch_polys<LN>(forward, p, T, limb_start, limb_count, cnt, st); break;
+        const size_t woff = (off * (size_t)limb_count) << T.logn;
+        u64* p = data + woff;
+        const u64* pm = mul ? mul + woff : nullptr;
+#define MFHE_CASE(LN) case LN: err = launch_polys<LN>(forward, p, T, limb_start, limb_count, cnt, st, pm, mu); break;
         switch (T.logn) {
             MFHE_CASE(12) MFHE_CASE(13) MFHE_CASE(14) MFHE_CASE(15) MFHE_CASE(16) MFHE_CASE(17)
             default: return cudaErrorInvalidValue;

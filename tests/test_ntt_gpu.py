@@ -103,6 +103,45 @@ def test_polymul_n4096_vs_schoolbook(m, cuda_device):
         assert (to_host(da).reshape(-1) == ref).all()
 
 
+def test_mul_intt_fused(m, cuda_device):
+    """mfhe_ntt_mul_intt (product applied inside the first inverse pass) == schoolbook at N = 4096 (BASELINE config 1a),
+    == the unfused NTT / pointwise / INTT sequence word for word at N = 2^16 with an odd batch (PB groups + remainder),
+    operand reuse through b_is_ntt, and the small-n composition."""
+    q, logn, n = 1152921504606830593, 12, 4096
+    plan = m.NttPlan(logn, [q])
+    a, b = O.synth_polys(1, 1, [q], n), O.synth_polys(2, 1, [q], n)
+    da, db = to_dev(a, cuda_device), to_dev(b, cuda_device)
+    plan.mul_intt_(da, db)
+    ref = np.zeros(n, dtype=np.uint64)
+    O.lib().mfo_schoolbook_mul(a.reshape(-1).copy(), b.reshape(-1).copy(), ref, n, q, q - 1)
+    assert (to_host(da).reshape(-1) == ref).all()
+    dbn = to_dev(b, cuda_device); plan.forward_(dbn)
+    assert (to_host(db) == to_host(dbn)).all()                      # b is left in NTT form
+    for logn, L, batch in ((16, 3, 3), (13, 2, 5)):
+        n = 1 << logn
+        mods = O.coeff_modulus_create(n, 60 if logn == 16 else 50, L)
+        plan = m.NttPlan(logn, mods)
+        a, b = O.synth_polys(3, batch, mods, n), O.synth_polys(4, batch, mods, n)
+        ua, ub = to_dev(a, cuda_device), to_dev(b, cuda_device)
+        plan.forward_(ua); plan.forward_(ub); plan.mul(ua, ub, out=ua); plan.inverse_(ua)
+        fa, fb = to_dev(a, cuda_device), to_dev(b, cuda_device)
+        plan.mul_intt_(fa, fb)
+        assert (to_host(fa) == to_host(ua)).all() and (to_host(fb) == to_host(ub)).all()
+        ga = to_dev(a, cuda_device)
+        plan.mul_intt_(ga, fb, b_is_ntt=True)                        # reuse the transformed operand
+        assert (to_host(ga) == to_host(ua)).all()
+    q64 = 17592186435073                                             # n = 64, the reference's first modulus
+    plan = m.NttPlan(6, [q64])
+    a, b = O.synth_polys(5, 7, [q64], 64), O.synth_polys(6, 7, [q64], 64)
+    fa, fb = to_dev(a, cuda_device), to_dev(b, cuda_device)
+    plan.mul_intt_(fa, fb)
+    got = to_host(fa).reshape(7, 64)
+    for i in range(7):
+        ref = np.zeros(64, dtype=np.uint64)
+        O.lib().mfo_schoolbook_mul(a.reshape(7, 64)[i].copy(), b.reshape(7, 64)[i].copy(), ref, 64, q64, q64 - 1)
+        assert (got[i] == ref).all()
+
+
 def test_limb_window_and_chunking(m, cuda_device):
     logn, n, L = 13, 8192, 6
     mods = O.coeff_modulus_create(n, 55, L)
