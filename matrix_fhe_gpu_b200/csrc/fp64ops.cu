@@ -9,6 +9,7 @@
 //                 batched_encoder.cu:192-196, HE.cu:1676-1679)
 //   quantize      llround(z * delta) mod q_l (batched_encoder.cu:125-152, encoder.cu:36-50)
 // fp64 results agree with the reference within summation-order round-off (tolerance-checked).
+#include <cstdlib>
 #include "ctx.h"
 
 namespace mfhe {
@@ -249,13 +250,100 @@ wdft_ipair_kernel(const double2* __restrict__ tabh, const int2* __restrict__ pai
     }
 }
 
+// ---- the same two forms on the FP64 tensor cores (mma.sync m8n8k4 .f64: 256 FMAs per warp instruction) ----------------
+// Both conjugate-pair forms are REAL GEMMs.  Forward: rows (pair, c | d) x columns (col, a | b); the C fragment of a
+// thread (row lane/4, two adjacent columns) is then (S.a, S.b) of one complex column, and with the c rows in m-tiles
+// 0-1 and the d rows in m-tiles 2-3 of a warp the same thread also holds the matching d sums: the four sums of a pair
+// meet in one thread.  Fragments (PTX ISA, mma.m8n8k4 .f64): A[row = lane/4][k = lane%4], B[k = lane%4][col = lane/4],
+// C[row = lane/4][cols 2 (lane%4) + {0, 1}].  Shared rows are padded to stride % 32 == 8 doubles: a fragment load of a
+// warp (4 k-rows x 8 consecutive doubles) then covers 32 distinct 8-byte slots, the 2-wavefront minimum.
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+constexpr int MSP = PTP + 8, MSX = 2 * DTC + 8;      // padded row strides (doubles)
+
+// CTA tile = 32 pairs x 64 complex columns, 8 warps = 2 (16 pairs) x 4 (16 columns)
+template <int IN, int OUT>
+__global__ void __launch_bounds__(DTHREADS, 2)
+wdft_opair_dmma_kernel(const double2* __restrict__ tabh, const int2* __restrict__ pairs, const void* __restrict__ in0,
+                       const void* __restrict__ in1, void* __restrict__ out0, void* __restrict__ out1, int phi, int cols) {
+    __shared__ __align__(16) double sC[2][DTK][MSP];
+    __shared__ __align__(16) double sD[2][DTK][MSP];
+    __shared__ __align__(16) double sX[2][DTK][MSX];
+    const int hp = phi >> 1;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, wp = warp & 1, wc = warp >> 1;
+    const int p0 = blockIdx.y * PTP, c0 = blockIdx.x * DTC;
+    const int lk = t >> 5, lp = t & 31, lg = (t & 31) << 1;
+    double2 rt, ri[2];
+    auto fetch = [&](int k0) {
+        const int i = k0 + lk;
+        rt = (i < phi && p0 + lp < hp) ? __ldg(tabh + (size_t)i * hp + p0 + lp) : make_double2(0, 0);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int c = c0 + lg + j;
+            ri[j] = (i < phi && c < cols) ? wdft_load<IN>(in0, in1, (size_t)i * cols + c) : make_double2(0, 0);
+        }
+    };
+    auto stash = [&](int buf) {
+        sC[buf][lk][lp] = rt.x; sD[buf][lk][lp] = rt.y;
+        *reinterpret_cast<double4*>(&sX[buf][lk][2 * lg]) = make_double4(ri[0].x, ri[0].y, ri[1].x, ri[1].y);
+    };
+    double aC[2][4][2], aD[2][4][2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) aC[i][j][0] = aC[i][j][1] = aD[i][j][0] = aD[i][j][1] = 0.0;
+    fetch(0); stash(0);
+    __syncthreads();
+    const int ktiles = (phi + DTK - 1) / DTK;
+    const int fk = lane & 3, fr = lane >> 2;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * DTK);
+#pragma unroll
+        for (int kk = 0; kk < DTK / 4; ++kk) {
+            double fc[2], fd[2], fb[4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                fc[i] = sC[buf][kk * 4 + fk][wp * 16 + i * 8 + fr];
+                fd[i] = sD[buf][kk * 4 + fk][wp * 16 + i * 8 + fr];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fb[j] = sX[buf][kk * 4 + fk][wc * 32 + j * 8 + fr];
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { dmma884(aC[i][j], fc[i], fb[j]); dmma884(aD[i][j], fd[i], fb[j]); }
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int p = p0 + wp * 16 + i * 8 + fr;
+        if (p >= hp) continue;
+        const int2 ow = pairs[p];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = c0 + wc * 16 + j * 4 + fk;
+            if (c >= cols) continue;
+            const double ca = aC[i][j][0], cb = aC[i][j][1], da = aD[i][j][0], db = aD[i][j][1];
+            wdft_store<OUT>(out0, out1, (size_t)ow.x * cols + c, ca - db, cb + da);
+            wdft_store<OUT>(out0, out1, (size_t)ow.y * cols + c, ca + db, cb - da);
+        }
+    }
+}
+
 template <int IN, int OUT>
 static cudaError_t wdft_dispatch(const WdftTab& w, const void* in0, const void* in1, void* out0, void* out1, int phi,
                                  int cols, cudaStream_t st) {
     const int hp = phi / 2;
     if (w.mode == 1 && w.half && w.pairs) {
         dim3 grid((cols + DTC - 1) / DTC, (hp + PTP - 1) / PTP);
-        wdft_opair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+        static const bool dfma = std::getenv("MFHE_WDFT_DFMA") != nullptr;      // A/B switch: CUDA-core DFMA form
+        if (dfma) wdft_opair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+        else      wdft_opair_dmma_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
     } else if (w.mode == 2 && w.half && w.pairs) {
         dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
         wdft_ipair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
