@@ -335,6 +335,78 @@ wdft_opair_dmma_kernel(const double2* __restrict__ tabh, const int2* __restrict_
     }
 }
 
+// Inverse as a real GEMM: K runs over (pair, P | Q), B rows (pair, P) = (x + x', y + y'), (pair, Q) = (y' - y, x - x') per
+// complex column, so C[o][(col, re | im)] is the result itself.  CTA tile = 64 outputs x 64 columns, 8 warps = 2 (32
+// outputs) x 4 (16 columns), K tile = 4 pairs = 8 rows.
+constexpr int MSO = DTO + 8;
+template <int IN, int OUT>
+__global__ void __launch_bounds__(DTHREADS, 2)
+wdft_ipair_dmma_kernel(const double2* __restrict__ tabh, const int2* __restrict__ pairs, const void* __restrict__ in0,
+                       const void* __restrict__ in1, void* __restrict__ out0, void* __restrict__ out1, int phi, int cols) {
+    __shared__ __align__(16) double sA[2][DTK][MSO];
+    __shared__ __align__(16) double sB[2][DTK][MSX];
+    const int hp = phi >> 1;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, wo = warp & 1, wc = warp >> 1;
+    const int o0 = blockIdx.y * DTO, c0 = blockIdx.x * DTC;
+    const int lpl = t >> 6, lg = t & 63;
+    double2 rt, rs, rd;
+    auto fetch = [&](int pk0) {
+        const int p = pk0 + lpl;
+        rt = (p < hp && o0 + lg < phi) ? __ldg(tabh + (size_t)p * phi + o0 + lg) : make_double2(0, 0);
+        const int c = c0 + lg;
+        if (p < hp && c < cols) {
+            const int2 ww = pairs[p];
+            const double2 z = wdft_load<IN>(in0, in1, (size_t)ww.x * cols + c);
+            const double2 w = wdft_load<IN>(in0, in1, (size_t)ww.y * cols + c);
+            rs = make_double2(z.x + w.x, z.y + w.y);
+            rd = make_double2(w.y - z.y, z.x - w.x);
+        } else rs = rd = make_double2(0, 0);
+    };
+    auto stash = [&](int buf) {
+        sA[buf][2 * lpl][lg] = rt.x; sA[buf][2 * lpl + 1][lg] = rt.y;
+        *reinterpret_cast<double2*>(&sB[buf][2 * lpl][2 * lg]) = rs;
+        *reinterpret_cast<double2*>(&sB[buf][2 * lpl + 1][2 * lg]) = rd;
+    };
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    fetch(0); stash(0);
+    __syncthreads();
+    constexpr int PK = DTK / 2;                        // pairs per K tile
+    const int ktiles = (hp + PK - 1) / PK;
+    const int fk = lane & 3, fr = lane >> 2;
+    for (int kt = 0; kt < ktiles; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < ktiles) fetch((kt + 1) * PK);
+#pragma unroll
+        for (int kk = 0; kk < DTK / 4; ++kk) {
+            double fa[4], fb[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fa[i] = sA[buf][kk * 4 + fk][wo * 32 + i * 8 + fr];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fb[j] = sB[buf][kk * 4 + fk][wc * 32 + j * 8 + fr];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j], fa[i], fb[j]);
+        }
+        if (kt + 1 < ktiles) stash(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int o = o0 + wo * 32 + i * 8 + fr;
+        if (o >= phi) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int c = c0 + wc * 16 + j * 4 + fk;
+            if (c < cols) wdft_store<OUT>(out0, out1, (size_t)o * cols + c, acc[i][j][0], acc[i][j][1]);
+        }
+    }
+}
+
 template <int IN, int OUT>
 static cudaError_t wdft_dispatch(const WdftTab& w, const void* in0, const void* in1, void* out0, void* out1, int phi,
                                  int cols, cudaStream_t st) {
@@ -346,7 +418,9 @@ static cudaError_t wdft_dispatch(const WdftTab& w, const void* in0, const void* 
         else      wdft_opair_dmma_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
     } else if (w.mode == 2 && w.half && w.pairs) {
         dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
-        wdft_ipair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+        static const bool dfma = std::getenv("MFHE_WDFT_DFMA") != nullptr;
+        if (dfma) wdft_ipair_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
+        else      wdft_ipair_dmma_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.half, w.pairs, in0, in1, out0, out1, phi, cols);
     } else {
         dim3 grid((cols + DTC - 1) / DTC, (phi + DTO - 1) / DTO);
         wdft_gemm_kernel<IN, OUT><<<grid, DTHREADS, 0, st>>>(w.full, in0, in1, out0, out1, phi, cols);
