@@ -30,6 +30,9 @@
 #include "ctx.h"
 #include "wcrt_common.cuh"
 
+#ifndef MFHE_UMMA_PREFETCH
+#define MFHE_UMMA_PREFETCH 1      // chunks ahead of the loads that the producers prefetch into L2 (0.362 -> 0.355 ms)
+#endif
 #ifndef MFHE_UMMA_DBG
 #define MFHE_UMMA_DBG 0      // timing experiments only: 1 = no table copies, 2 = no input loads, 4 = no epilogue arithmetic
 #endif
@@ -288,8 +291,14 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
 #else
                 if (!f_ok[r]) { rb[2 * j] = 0; rb[2 * j + 1] = 0; }
                 else if constexpr (SRC == kSrcMem) {
-                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>((const u64*)a.in + (size_t)i * istride + f_off[r]));
+                    const u64* src = (const u64*)a.in + (size_t)i * istride + f_off[r];
+                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(src));
                     rb[2 * j] = v.x; rb[2 * j + 1] = v.y;
+#if MFHE_UMMA_PREFETCH
+                    // the rows this item needs MFHE_UMMA_PREFETCH chunks later (same tile): start them towards L2 now
+                    if (f_kt + MFHE_UMMA_PREFETCH * C::PG < kchunks)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(MFHE_UMMA_PREFETCH * C::PG * UKC) * istride));
+#endif
                 } else {
                     rb[2 * j] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r], f_q, f_mu);
                     rb[2 * j + 1] = wcrt_load_one<SRC>(a, i, f_l, f_c0 + ic[r] + 1, f_q, f_mu);
