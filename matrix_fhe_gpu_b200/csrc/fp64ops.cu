@@ -512,6 +512,100 @@ xy_sandwich_kernel(const double2* __restrict__ A, const double2* __restrict__ B,
 #pragma unroll
         for (int j = 0; j < R; ++j) O[(ty + 16 * i) * n + tx + 16 * j] = acc[i][j];
 }
+// n = 64 on the FP64 tensor cores.  A complex product C = A * M is the REAL GEMM
+//     [C interleaved (n x 2n)] = [Ar | Ai] (n x 2n)  x  [ M interleaved ; M' ] (2n x 2n),   M'[k][(j, re | im)] = (-Mi, Mr)[k][j],
+// and M' is just M read at the neighbouring part with a sign, so only M itself is staged.  One CTA per lane, 8 warps =
+// 2 (32 rows) x 4 (32 real columns), 16 MMAs per 8 fragment loads; both products run through the same code, the first
+// result goes back to shared memory as the (Tr | Ti) operand of the second.  Row strides: 132 doubles (== 4 mod 32) for
+// the row-major A operand, 136 (== 8 mod 32) for the k-major B operand: conflict-free fragment loads.
+constexpr int XSA = 132, XSM = 136;
+__global__ void __launch_bounds__(256)
+xy_sandwich_dmma64_kernel(const double2* __restrict__ A, const double2* __restrict__ B, const double2* __restrict__ in,
+                          double2* __restrict__ out) {
+    constexpr int n = 64;
+    extern __shared__ __align__(16) double sm_xd[];
+    double* sA = sm_xd;                    // [n][XSA]: (Ar | Ai), later (Tr | Ti)
+    double* sM = sm_xd + n * XSA;          // [n][XSM]: M interleaved, later B
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5, wr = warp & 1, wc = warp >> 1;
+    const int fk = lane & 3, fr = lane >> 2;
+    const double2* M = in + (size_t)blockIdx.x * n * n;
+    for (int e = t; e < n * n; e += 256) {
+        const int r = e >> 6, c = e & 63;
+        const double2 a = __ldg(A + e), m = M[e];
+        sA[r * XSA + c] = a.x; sA[r * XSA + n + c] = a.y;
+        *reinterpret_cast<double2*>(&sM[r * XSM + 2 * c]) = m;
+    }
+    __syncthreads();
+    double acc[4][4][2];
+    auto product = [&]() {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        const double* pa = sA + (wr * 32 + fr) * XSA + fk;
+        const int col = wc * 32 + fr;
+        const double sgn = (fr & 1) ? 1.0 : -1.0;                  // part 0 (re) of M' is -Mi
+#pragma unroll 4
+        for (int k4 = 0; k4 < n / 4; ++k4) {                       // K rows 0..n-1: (Ar, M)
+            double fa[4], fb[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fa[i] = pa[i * 8 * XSA + k4 * 4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fb[j] = sM[(k4 * 4 + fk) * XSM + col + j * 8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j], fa[i], fb[j]);
+        }
+#pragma unroll 4
+        for (int k4 = 0; k4 < n / 4; ++k4) {                       // K rows n..2n-1: (Ai, M')
+            double fa[4], fb[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) fa[i] = pa[i * 8 * XSA + n + k4 * 4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fb[j] = sgn * sM[(k4 * 4 + fk) * XSM + ((col + j * 8) ^ 1)];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j], fa[i], fb[j]);
+        }
+    };
+    product();                                                     // T = A * M
+    __syncthreads();
+    // C fragment: row wr*32 + i*8 + fr, complex column wc*16 + j*4 + fk, (re, im) = acc[i][j][0..1]
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = wr * 32 + i * 8 + fr, c = wc * 16 + j * 4 + fk;
+            sA[r * XSA + c] = acc[i][j][0]; sA[r * XSA + n + c] = acc[i][j][1];
+        }
+    for (int e = t; e < n * n; e += 256) {
+        const int r = e >> 6, c = e & 63;
+        *reinterpret_cast<double2*>(&sM[r * XSM + 2 * c]) = __ldg(B + e);
+    }
+    __syncthreads();
+    product();                                                     // out = T * B
+    double2* O = out + (size_t)blockIdx.x * n * n;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            O[(wr * 32 + i * 8 + fr) * n + wc * 16 + j * 4 + fk] = make_double2(acc[i][j][0], acc[i][j][1]);
+}
+static cudaError_t xy_sandwich_dmma64_launch(const double2* A, const double2* B, const double2* in, double2* out, int lanes,
+                                             cudaStream_t st) {
+    constexpr size_t smem = (size_t)64 * (XSA + XSM) * sizeof(double);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(xy_sandwich_dmma64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    xy_sandwich_dmma64_kernel<<<lanes, 256, smem, st>>>(A, B, in, out);
+    return cudaGetLastError();
+}
+
 template <int R>
 static cudaError_t xy_sandwich_launch_r(const double2* A, const double2* B, const double2* in, double2* out, int lanes,
                                         cudaStream_t st) {
@@ -531,7 +625,10 @@ cudaError_t xy_sandwich_launch(const double2* A, const double2* B, const double2
     switch (n) {
         case 16: return xy_sandwich_launch_r<1>(A, B, in, out, lanes, st);
         case 32: return xy_sandwich_launch_r<2>(A, B, in, out, lanes, st);
-        case 64: return xy_sandwich_launch_r<4>(A, B, in, out, lanes, st);
+        case 64: {
+            static const bool dfma = std::getenv("MFHE_XY_DFMA") != nullptr;      // A/B switch: CUDA-core version
+            return dfma ? xy_sandwich_launch_r<4>(A, B, in, out, lanes, st) : xy_sandwich_dmma64_launch(A, B, in, out, lanes, st);
+        }
         default: return cudaErrorInvalidValue;
     }
 }

@@ -56,6 +56,28 @@ def test_native_tables(G, Or):
     assert all((t[k] == r[k]).all() for k in t)
 
 
+def test_native_fp64_transforms_vs_oracle(G, Or, cuda_device):
+    """n = 64 XY sandwich and phi = 512 W-DFT (the FP64 tensor-core kernels) against the oracle's plain loops;
+    tolerance: 2^-40 relative to the largest magnitude (summation-order round-off only)."""
+    S, g = G
+    rng = np.random.default_rng(3)
+    lanes = 3
+    m = (rng.standard_normal(lanes * 4096) + 1j * rng.standard_normal(lanes * 4096)) * 1e3
+    for got, want in ((host(g.idft2(dev(m, cuda_device), lanes)), Or.xy_idft2(m, lanes)),
+                      (host(g.dft2(dev(m, cuda_device), lanes)), Or.xy_dft2(m, lanes))):
+        assert np.abs(got - want).max() <= 2.0 ** -40 * np.abs(want).max()
+    z = (rng.standard_normal(512 * 4096) + 1j * rng.standard_normal(512 * 4096)) * 1e3
+    got = host(g.wdft_forward_complex(dev(z, cuda_device))).reshape(512, 4096)
+    cols = [0, 1, 77, 4095]
+    want = Or.wdft_forward_complex(z).reshape(512, 4096)
+    assert np.abs(got[:, cols] - want[:, cols]).max() <= 2.0 ** -36 * np.abs(want[:, cols]).max()
+    zi = z.reshape(512, 4096)
+    gr, gi = g.wdft_inverse_pair(dev(zi.real.copy().reshape(-1), cuda_device), dev(zi.imag.copy().reshape(-1), cuda_device))
+    wr, wi = Or.wdft_inverse_pair(zi.real.copy().reshape(-1), zi.imag.copy().reshape(-1))
+    scale = max(np.abs(wr).max(), np.abs(wi).max())
+    assert max(np.abs(host(gr) - wr).max(), np.abs(host(gi) - wi).max()) <= 2.0 ** -30 * scale
+
+
 def test_native_reference_drivers(G, cuda_device):
     import torch
     S, g = G
