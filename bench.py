@@ -119,10 +119,20 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2):
                     r, q = g.encode_to_wntt_eval(m)
                     g.encrypt_pair(r, q, sk, cr, ci)
                     g.decrypt_and_decode(cr, ci, sk, dec)
-            ms = timed(pipe, 2)
+
+            def pipe_fused():                    # same ciphertext words, message and error share a W-CRT
+                for _ in range(pairs_per_rank):
+                    g.encode_encrypt_pair(m, sk, cr, ci)
+                    g.decrypt_and_decode(cr, ci, sk, dec)
+            ms3 = timed(pipe, 2)
+            ms = timed(pipe_fused, 2)
+            errf = float((dec - m).abs().max())
+            assert errf < 1e-3, errf
             out[tag] = {"pairs_per_s": world * pairs_per_rank / (ms * 1e-3), "ciphertexts_per_s": 2 * world * pairs_per_rank / (ms * 1e-3),
-                        "ms_per_pair": ms / pairs_per_rank, "pairs_per_rank_per_step": pairs_per_rank, "max_err": err,
-                        "note": "encode -> encrypt_pair -> decrypt_and_decode, one (re, im) pair = 2 ciphertexts of 768 MiB"}
+                        "ms_per_pair": ms / pairs_per_rank, "ms_per_pair_three_calls": ms3 / pairs_per_rank,
+                        "pairs_per_rank_per_step": pairs_per_rank, "max_err": max(err, errf),
+                        "note": "mfhe_encode_encrypt_pair -> decrypt_and_decode (three_calls: encode -> encrypt_pair -> "
+                                "decrypt_and_decode, identical ciphertexts), one (re, im) pair = 2 ciphertexts of 768 MiB"}
         del g
         torch.cuda.empty_cache()
     return out

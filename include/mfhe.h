@@ -220,6 +220,11 @@ int mfhe_encrypt_pair(mfhe_ctx *ctx, const uint64_t *d_m_re, const uint64_t *d_m
 int mfhe_encrypt_pair_with(mfhe_ctx *ctx, const uint64_t *d_m_re, const uint64_t *d_m_im, const uint64_t *d_sk,
                            const uint64_t *d_a_coeff, const uint64_t *d_e_re, const uint64_t *d_e_im,
                            uint64_t *d_ct_re, uint64_t *d_ct_im, void *stream);
+/* encode_to_wntt_eval followed by encrypt_pair (batched_encoder.cu:161-228 + HE.cu:1455-1552) as ONE call with
+ * identical ciphertext words: message and error are summed in the W-coeff domain and share a W-CRT (3 instead
+ * of 4 per pair).  d_msg: phi * n^2 complex fp64. */
+int mfhe_encode_encrypt_pair(mfhe_ctx *ctx, const double *d_msg, const uint64_t *d_sk, uint64_t *d_ct_re,
+                             uint64_t *d_ct_im, void *stream);
 /* encrypt (HE.cu:1370-1453) */
 int mfhe_encrypt(mfhe_ctx *ctx, const uint64_t *d_m, const uint64_t *d_sk, uint64_t *d_ct, void *stream);
 /* decrypt_to_eval (HE.cu:1553-1601; out_layout POLY) / decrypt_to_eval_matrix (:1603-1617; MATRIX) */

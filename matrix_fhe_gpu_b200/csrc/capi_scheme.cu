@@ -515,6 +515,47 @@ extern "C" int mfhe_encrypt_pair_with(mfhe_ctx* c, const uint64_t* m_re, const u
     if (!a_coeff || !e_re || !e_im || !ct_im) return fail(MFHE_EINVAL, "encrypt_pair_with: NULL argument");
     return encrypt_core(c, m_re, m_im, sk, kSrcMem, a_coeff, kSrcMem, e_re, e_im, ct_re, ct_im, s, "encrypt_pair_with");
 }
+// Fused BatchedEncoder::encode_to_wntt_eval + encrypt_pair (batched_encoder.cu:161-228, HE.cu:1455-1552): the same
+// ciphertext words as the two calls in sequence, but the quantised message and the error are added in the W-coeff
+// domain (two int64 planes) and transformed together -- 3 W-CRTs instead of 4, and the encoded message never
+// makes a round trip through HBM on its own: the W-CRT writes (m + e) straight into the b halves, the row kernel
+// then subtracts INTT(NTT(a) (.) s) in place.
+extern "C" int mfhe_encode_encrypt_pair(mfhe_ctx* c, const double* msg, const uint64_t* sk, uint64_t* ct_re, uint64_t* ct_im,
+                                        void* s) {
+    if (!c || !msg || !sk || !ct_re || !ct_im) return fail(MFHE_EINVAL, "encode_encrypt_pair: NULL argument");
+    c->arena_reset();
+    const size_t T = c->T(), total = (size_t)c->phi * c->n2(), lanes_bytes = total * sizeof(double2);
+    double2* xy = (double2*)c->take(lanes_bytes);
+    double2* wc = (double2*)c->take(lanes_bytes);
+    u64* scratch = (u64*)c->take(T * 8);
+    if (!xy || !wc || !scratch) return fail(MFHE_ENOMEM, "encode_encrypt_pair: arena too small");
+    cudaStream_t st = S(s);
+    cudaError_t e = xy_sandwich_launch(c->d_xyVinv, c->d_xyVinvT, (const double2*)msg, xy, c->n, c->phi, st);
+    if (e == cudaSuccess) e = wdft_launch(wdft_tab(c, true), xy, wc, c->phi, (int)c->n2(), st);
+    long long* qre = (long long*)xy;
+    long long* qim = qre + total;
+    if (e == cudaSuccess) e = llround_noise_planes_launch(wc, qre, qim, total, c->delta, st);
+    for (int part = 0; part < 2 && e == cudaSuccess; ++part) {          // (m + e) -> W-eval, into the b halves
+        WcrtArgs a = wcrt_args(c, false);
+        a.in = part ? qim : qre; a.out = (u64*)(part ? ct_im : ct_re);
+        a.source = kSrcI64; a.out_layout = MFHE_LAYOUT_MATRIX; a.scratch = scratch;
+        e = wcrt_launch(a, st);
+    }
+    if (e == cudaSuccess) {                                              // a: uniform W-coeff -> W-eval, both a halves
+        WcrtArgs a = wcrt_args(c, false);
+        a.source = kSrcUniform; a.in = nullptr; a.out = (u64*)ct_re + T; a.out2 = (u64*)ct_im + T; a.scratch = scratch;
+        e = wcrt_launch(a, st);
+    }
+    if (e == cudaSuccess) {
+        RowArgs r;
+        r.a = (const u64*)ct_re + T; r.s = (const u64*)sk;
+        r.m0 = (const u64*)ct_re; r.o0 = (u64*)ct_re;
+        r.m1 = (const u64*)ct_im; r.o1 = (u64*)ct_im;
+        r.subtract = 1; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
+        e = xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+    }
+    return done(e, "encode_encrypt_pair");
+}
 extern "C" int mfhe_encrypt(mfhe_ctx* c, const uint64_t* m, const uint64_t* sk, uint64_t* ct, void* s) {
     return encrypt_core(c, m, nullptr, sk, kSrcUniform, nullptr, kSrcGauss, nullptr, nullptr, ct, nullptr, s, "encrypt");
 }

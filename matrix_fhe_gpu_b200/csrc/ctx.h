@@ -83,6 +83,8 @@ struct WcrtArgs {
 cudaError_t wcrt_launch(const WcrtArgs& a, cudaStream_t st);
 // kSrcGauss input: int8 noise value of every logical coefficient [phi][cols]
 cudaError_t gauss_table_launch(signed char* out, int phi, int cols, cudaStream_t st);
+cudaError_t llround_noise_planes_launch(const double2* in, long long* re, long long* im, size_t total, double delta,
+                                        cudaStream_t st);
 
 // ---- fp64 complex kernels (fp64ops.cu) --------------------------------------------------------------
 // out[o][col] = sum_i tab[i][o] * in[i][col], phi x phi table, cols columns

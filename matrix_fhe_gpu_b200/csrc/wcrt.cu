@@ -71,6 +71,24 @@ cudaError_t gauss_table_launch(signed char* out, int phi, int cols, cudaStream_t
     return cudaGetLastError();
 }
 
+// fused encode + encrypt: llround(z * delta) + e of every value as two int64 planes, e = the reference's centred
+// gaussian of the logical coefficient (one draw shared by the re and im ciphertexts, HE.cu:1516-1517).  The W-CRT
+// is linear, Wcrt(m) + Wcrt(e) = Wcrt(m + e) mod q, so the error term needs no transform of its own.
+__global__ void llround_noise_planes_kernel(const double2* __restrict__ in, long long* __restrict__ re,
+                                            long long* __restrict__ im, size_t total, double delta) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const double2 z = in[i];
+    const long long g = gaussian_noise_value((u64)i);
+    re[i] = llround(z.x * delta) + g;
+    im[i] = llround(z.y * delta) + g;
+}
+cudaError_t llround_noise_planes_launch(const double2* in, long long* re, long long* im, size_t total, double delta,
+                                        cudaStream_t st) {
+    llround_noise_planes_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, re, im, total, delta);
+    return cudaGetLastError();
+}
+
 template <int SRC, bool SPLIT>
 __global__ void __launch_bounds__(WTHREADS)
 wcrt_gemm_kernel(const WcrtArgs a) {

@@ -62,6 +62,7 @@ def _L():
         "mfhe_sample_ternary": [_vp, _vp, _vp], "mfhe_keygen": [_vp, _vp, _vp],
         "mfhe_encrypt_pair": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
         "mfhe_encrypt_pair_with": [_vp] * 10,
+        "mfhe_encode_encrypt_pair": [_vp] * 6,
         "mfhe_encrypt": [_vp, _vp, _vp, _vp, _vp],
         "mfhe_decrypt_to_eval": [_vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_decrypt_decode": [_vp, _vp, _vp, _vp, _vp, _vp],
@@ -310,6 +311,14 @@ class Context:
         ct_re = self._new(2 * self.T, like=m_re); ct_im = self._new(2 * self.T, like=m_re)
         check(_L().mfhe_encrypt_pair_with(self._h, _dev_ptr(m_re), _dev_ptr(m_im), _dev_ptr(sk), _dev_ptr(a), _dev_ptr(e_re),
                                           _dev_ptr(e_im), _dev_ptr(ct_re), _dev_ptr(ct_im), _stream_handle()))
+        return ct_re, ct_im
+
+    def encode_encrypt_pair(self, msg, sk, ct_re=None, ct_im=None):
+        """encode_to_wntt_eval + encrypt_pair fused (same ciphertext words; message and error share a W-CRT)."""
+        ct_re = self._new(2 * self.T) if ct_re is None else ct_re
+        ct_im = self._new(2 * self.T) if ct_im is None else ct_im
+        check(_L().mfhe_encode_encrypt_pair(self._h, _any_ptr(msg), _dev_ptr(sk), _dev_ptr(ct_re), _dev_ptr(ct_im),
+                                            _stream_handle()))
         return ct_re, ct_im
 
     def encrypt(self, m, sk):

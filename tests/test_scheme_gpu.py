@@ -340,6 +340,25 @@ def test_full_pipeline_roundtrip(S, cuda_device, name):
 
 
 @pytest.mark.parametrize("name", list(SHAPES))
+def test_encode_encrypt_fused_bit_exact(S, cuda_device, name):
+    """mfhe_encode_encrypt_pair == encode_to_wntt_eval followed by encrypt_pair, word for word (the W-CRT is linear,
+    so message and error may share a transform), and against the oracle's integer core fed with the GPU's encoding."""
+    g, o = ctxs(S, name)
+    sk = g.generate_secret_key()
+    for kind in ("e2e", "uniform"):
+        m = dev(message(o, kind), cuda_device)
+        re, im = g.encode_to_wntt_eval(m)
+        cr, ci = g.encrypt_pair(re, im, sk)
+        fr, fi = g.encode_encrypt_pair(m, sk)
+        assert (host(fr) == host(cr)).all() and (host(fi) == host(ci)).all()
+    ge = host(g.sample_gaussian())
+    ocr, oci = o.encrypt_pair_with(host(re), host(im), host(sk), o.sample_uniform(), ge, ge)
+    assert (host(fr) == ocr).all() and (host(fi) == oci).all()
+    out = host(g.decrypt_and_decode(fr, fi, sk))
+    assert np.abs(out - message(o, "uniform")).max() < 1e-4
+
+
+@pytest.mark.parametrize("name", list(SHAPES))
 def test_trace_and_glperm(S, cuda_device, name):
     g, o = ctxs(S, name)
     rng = np.random.default_rng(20)

@@ -78,6 +78,19 @@ def test_native_fp64_transforms_vs_oracle(G, Or, cuda_device):
     assert max(np.abs(host(gr) - wr).max(), np.abs(host(gi) - wi).max()) <= 2.0 ** -30 * scale
 
 
+def test_native_encode_encrypt_fused(G, cuda_device):
+    """Native shape: the fused encode + encrypt call writes the same 4 x 176 MiB of ciphertext words as the two calls."""
+    import torch
+    S, g = G
+    sk = g.generate_secret_key()
+    m = dev(msg("e2e"), cuda_device)
+    re, im = g.encode_to_wntt_eval(m)
+    cr, ci = g.encrypt_pair(re, im, sk)
+    fr, fi = g.encode_encrypt_pair(m, sk)
+    assert torch.equal(fr, cr) and torch.equal(fi, ci)
+    assert np.abs(host(g.decrypt_and_decode(fr, fi, sk)) - msg("e2e")).max() < 1e-3
+
+
 def test_native_reference_drivers(G, cuda_device):
     import torch
     S, g = G

@@ -42,6 +42,7 @@ rows = [
     ("wcrt_inverse", lambda: g.wntt_inverse_matrix(a)),
     ("encode", lambda: g.encode_to_wntt_eval(m)),
     ("encrypt_pair", lambda: g.encrypt_pair(re, im, sk, cr, ci)),
+    ("encode_encrypt_pair (fused)", lambda: g.encode_encrypt_pair(m, sk, cr, ci)),
     ("decrypt_to_eval (1 ct)", lambda: g.decrypt_to_eval(cr, sk)),
     ("decrypt_and_decode", lambda: g.decrypt_and_decode(cr, ci, sk, out)),
     ("keygen", lambda: g.generate_secret_key()),
