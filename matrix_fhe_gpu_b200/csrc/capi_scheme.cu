@@ -577,8 +577,12 @@ extern "C" int mfhe_decrypt_decode(mfhe_ctx* c, const uint64_t* ct_re, const uin
     u64* mr = (u64*)c->take(c->T() * 8);
     u64* mi = (u64*)c->take(c->T() * 8);
     if (!mr || !mi) return fail(MFHE_ENOMEM, "decrypt_decode: arena too small");
-    cudaError_t e = decrypt_rows(c, (const u64*)ct_re, (const u64*)sk, mr, MFHE_LAYOUT_MATRIX, S(s));
-    if (e == cudaSuccess) e = decrypt_rows(c, (const u64*)ct_im, (const u64*)sk, mi, MFHE_LAYOUT_MATRIX, S(s));
+    // both ciphertexts in one launch: rows whose a parts agree (always, for a pair made by encrypt_pair) share t
+    RowArgs r;
+    r.a = (const u64*)ct_re + c->T(); r.a1 = (const u64*)ct_im + c->T(); r.s = (const u64*)sk;
+    r.m0 = (const u64*)ct_re; r.o0 = mr; r.m1 = (const u64*)ct_im; r.o1 = mi;
+    r.o_layout = MFHE_LAYOUT_MATRIX; r.subtract = 0; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
+    cudaError_t e = xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, S(s));
     if (e == cudaSuccess) e = decode_tail(c, mr, mi, MFHE_LAYOUT_MATRIX, (double2*)out, S(s));
     if (e == cudaErrorMemoryAllocation) return fail(MFHE_ENOMEM, "decrypt_decode: arena too small");
     return done(e, "decrypt_decode");

@@ -123,6 +123,7 @@ cudaError_t big_pair_to_complex_launch(const u64* re_mag, const uint8_t* re_neg,
 // ---- scheme kernels (scheme.cu) ------------------------------------------------------------------------
 struct RowArgs {                 // one launch over all phi*L*n rows of n coefficients
     const u64 *a = nullptr, *s = nullptr;          // a rows (layout a_layout), key [w][l][x]
+    const u64 *a1 = nullptr;                       // optional: the second component's own a (compared with a row by row)
     const u64 *m0 = nullptr, *e0 = nullptr; u64* o0 = nullptr;   // out0 = m0 -/+ t + e0
     const u64 *m1 = nullptr, *e1 = nullptr; u64* o1 = nullptr;   // optional second component
     int a_layout = 0, m_layout = 0, e_layout = 0, o_layout = 0;

@@ -24,10 +24,7 @@ __device__ __forceinline__ size_t row_offset(int layout, u32 w, u32 l, u32 y, in
 #ifndef MFHE_XROW_MINB
 #define MFHE_XROW_MINB 4
 #endif
-#ifndef MFHE_XROW_PREFETCH
-#define MFHE_XROW_PREFETCH 0
-#endif
-template <int LOGN>
+template <int LOGN, bool DUAL>
 __global__ void __launch_bounds__(256, MFHE_XROW_MINB)
 xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_tab, size_t rows) {
     using Net = SmallNet<LOGN>;
@@ -40,17 +37,22 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
     const u64 q = T.moduli[l], q2 = 2 * q;
     const ulonglong2 mu = mu_tab[l];
     u64* sm = sm_all + pib * STRIDE;
-    u64 v[8];
-#if MFHE_XROW_PREFETCH
-    // the first message row is fetched before the transforms so that its latency hides behind them
-    u64 pm[8];
-    {
-        const u64* m = r.m0 + row_offset(r.m_layout, w, l, y, r.n, r.limbs) + Net::out_base(u);
+    const size_t ao = row_offset(r.a_layout, w, l, y, r.n, r.limbs);
+    // Two components may come with their own a (decrypt of an (re, im) pair: a1).  encrypt_pair stores the SAME a in
+    // both ciphertexts (HE.cu:1538-1545), so the rows are compared while they are loaded and, when every row of the
+    // warp agrees, t = INTT(NTT(a) (.) s) is computed once and used for both; any difference -> second pass over a1.
+    bool shared_t = true;
+    if constexpr (DUAL) {
+        const u32 e0 = deposit3(u, Net::FP0);
+        bool eq = true;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) pm[j] = m[j << Net::PL];
+        for (int j = 0; j < 8; ++j) eq &= r.a[ao + e0 + (j << Net::FP0)] == r.a1[ao + e0 + (j << Net::FP0)];
+        shared_t = __all_sync(__activemask(), eq);
     }
-#endif
-    Net::forward(v, r.a + row_offset(r.a_layout, w, l, y, r.n, r.limbs), sm, u, T.tw + ((size_t)l << LOGN), q, q2);
+    const int passes = (DUAL && !shared_t) ? 2 : 1;       // DUAL = false: one pass, compile-time
+    for (int pass = 0; pass < passes; ++pass) {
+    u64 v[8];
+    Net::forward(v, ((DUAL && pass) ? r.a1 : r.a) + ao, sm, u, T.tw + ((size_t)l << LOGN), q, q2);
     {
         const u64* s = r.s + ((size_t)wl << LOGN) + 8 * u;      // key is stored in the same bit-reversed order
         const ulonglong2 s0 = __ldg((const ulonglong2*)s), s1 = __ldg((const ulonglong2*)s + 1),
@@ -64,6 +66,7 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
     const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)l << LOGN), q, q2, T.ninv[l], T.w1n[l]);
 #pragma unroll
     for (int comp = 0; comp < 2; ++comp) {
+        if (passes == 2 && comp != pass) continue;
         const u64* m = comp ? r.m1 : r.m0;
         const u64* er = comp ? r.e1 : r.e0;
         u64* o = comp ? r.o1 : r.o0;
@@ -73,15 +76,13 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const u32 pos = e + (j << Net::PL);
-#if MFHE_XROW_PREFETCH
-            u64 x = comp ? m[mo + pos] : pm[j];
-#else
             u64 x = m[mo + pos];
-#endif
             if (r.subtract) { x = sub_mod(x, v[j], q); if (er) x = add_mod(x, er[eo + pos], q); }
             else x = add_mod(x, v[j], q);
             o[oo + pos] = x;
         }
+    }
+    if (pass + 1 < passes) __syncwarp();                       // the shared tile is reused by the second pass
     }
 }
 
@@ -90,7 +91,8 @@ cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulon
 #define MFHE_ROW_CASE(LN)                                                                       \
     case LN: {                                                                                  \
         constexpr int PPB = 256 / ((1 << LN) / 8);                                              \
-        xrow_mul_s_kernel<LN><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
+        if (r.a1 && r.o1) xrow_mul_s_kernel<LN, true><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
+        else xrow_mul_s_kernel<LN, false><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
         break; }
     switch (T.logn) {
         MFHE_ROW_CASE(4) MFHE_ROW_CASE(5) MFHE_ROW_CASE(6) MFHE_ROW_CASE(7) MFHE_ROW_CASE(8)

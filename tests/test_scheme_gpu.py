@@ -359,6 +359,28 @@ def test_encode_encrypt_fused_bit_exact(S, cuda_device, name):
 
 
 @pytest.mark.parametrize("name", list(SHAPES))
+def test_decrypt_pair_shared_and_distinct_a(S, cuda_device, name):
+    """decrypt_and_decode runs both ciphertexts through one row-kernel launch and shares t = INTT(NTT(a) s) between
+    them when their a parts agree (encrypt_pair stores the same a twice, HE.cu:1538-1545).  Equal a, entirely different
+    a and a single differing word must all give exactly what two separate decrypt_to_eval calls give."""
+    import torch
+    g, o = ctxs(S, name)
+    sk = g.generate_secret_key()
+    m = dev(message(o, "uniform"), cuda_device)
+    re, im = g.encode_to_wntt_eval(m)
+    cr, ci = g.encrypt_pair(re, im, sk)
+    e2 = g.sample_gaussian()
+    _, ci2 = g.encrypt_pair_with(re, im, sk, dev(rand_polyset(o, 31), cuda_device), e2, e2)
+    ci3 = ci.clone()
+    ci3[o.T + 5] = 1 if int(ci3[o.T + 5]) != 1 else 2
+    for x, y in ((cr, ci), (cr, ci2), (cr, ci3), (ci2, cr)):
+        want = g.decode_eval_pair(g.decrypt_to_eval(x, sk, S.MATRIX), g.decrypt_to_eval(y, sk, S.MATRIX), S.MATRIX)
+        got = g.decrypt_and_decode(x, y, sk)
+        assert torch.equal(torch.view_as_real(got), torch.view_as_real(want))
+    assert np.abs(host(g.decrypt_and_decode(cr, ci, sk)) - message(o, "uniform")).max() < 1e-4
+
+
+@pytest.mark.parametrize("name", list(SHAPES))
 def test_trace_and_glperm(S, cuda_device, name):
     g, o = ctxs(S, name)
     rng = np.random.default_rng(20)

@@ -19,5 +19,8 @@ for rep in range(2):
     cr, ci = g.encrypt_pair(re, im, sk)
     torch.cuda.synchronize(); print("== decrypt_decode", flush=True)
     out = g.decrypt_and_decode(cr, ci, sk)
+    torch.cuda.synchronize(); print("== encode_encrypt_pair (fused)", flush=True)
+    fr, fi = g.encode_encrypt_pair(m, sk)
     torch.cuda.synchronize()
+    assert torch.equal(fr, cr) and torch.equal(fi, ci)
 print("max_err", float((out - m).abs().max()))
