@@ -146,7 +146,36 @@ class ClockSampler:
     def __init__(self, index: int):
         self.rows, self.proc, self.index = [], None, index
 
+    def _nvml_loop(self):
+        import pynvml as nv
+        bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self.halt.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+                rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.nv_rows.append((float(sm), float(mx), [k for k, b in bits.items() if rs & b]))
+            except Exception:
+                pass
+            self.halt.wait(0.005)
+
     def start(self):
+        # NVML in-process (5 ms period: short runs, e.g. the multi-GPU scaling points, still get samples);
+        # nvidia-smi -lms 50 as the fallback
+        self.nv_rows, self.halt = [], threading.Event()
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].strip().isdigit() else self.index
+            self.h = nv.nvmlDeviceGetHandleByIndex(idx)
+            nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.t = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.t.start()
+            self.proc = "nvml"
+            return
+        except Exception:
+            pass
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "50"],
@@ -163,6 +192,12 @@ class ClockSampler:
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.proc == "nvml":
+            self.halt.set(); self.t.join(timeout=2)
+            sm = [r[0] for r in self.nv_rows]; mx = [r[1] for r in self.nv_rows]
+            reasons = sorted({x for r in self.nv_rows for x in r[2]})
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                    "reasons": reasons, "samples": len(sm), "source": "nvml, 5 ms period"}
         time.sleep(0.06)
         self.proc.terminate()
         self.t.join(timeout=2)
