@@ -1,6 +1,7 @@
 // capi_scheme.cu -- C ABI (include/mfhe.h) of the matrix pipeline: context, W-CRT, W-DFT, XY
 // embedding, CRT, encode / decode, samplers, keygen, encrypt / decrypt, ct ops, trace, GL perm.
 // Host-side orchestration only; the kernels live in wcrt.cu, fp64ops.cu, crt.cu, scheme.cu.
+#include <cstdlib>
 #include <algorithm>
 #include <cstring>
 #include <new>
@@ -607,6 +608,12 @@ extern "C" int mfhe_trace_map(mfhe_ctx* c, const uint64_t* Br, const uint64_t* B
 extern "C" int mfhe_trace_gemm(mfhe_ctx* c, const uint64_t* Ar, const uint64_t* Ai, const uint64_t* Bpr, const uint64_t* Bpi,
                                uint64_t* Cr, uint64_t* Ci, int batch, void* s) {
     if (!c || !Ar || !Ai || !Bpr || !Bpi || !Cr || !Ci || batch < 1) return fail(MFHE_EINVAL, "trace_gemm: bad argument");
+    // n = 64 and moduli below 2^48: int8 digit GEMMs on the tensor cores (trace_tc.cu); MFHE_TRACE_PATH=c pins the
+    // CUDA-core kernel (A/B and parity tests)
+    static const bool pin_cuda_core = [] { const char* e = std::getenv("MFHE_TRACE_PATH"); return e && e[0] == 'c'; }();
+    if (!pin_cuda_core && trace_gemm_tc_eligible(c->n, c->L, c->ndig.data()))
+        return done(trace_gemm_tc_launch((const u64*)Ar, (const u64*)Ai, (const u64*)Bpr, (const u64*)Bpi, (u64*)Cr, (u64*)Ci,
+                                         c->d_moduli, c->d_mu, c->ndig.data(), c->L, batch, S(s)), "trace_gemm");
     return done(trace_gemm_launch((const u64*)Ar, (const u64*)Ai, (const u64*)Bpr, (const u64*)Bpi, (u64*)Cr, (u64*)Ci,
                                   c->d_moduli, c->d_mu, c->n, c->L, batch, S(s)), "trace_gemm");
 }

@@ -91,6 +91,27 @@ def test_native_encode_encrypt_fused(G, cuda_device):
     assert np.abs(host(g.decrypt_and_decode(fr, fi, sk)) - msg("e2e")).max() < 1e-3
 
 
+def test_native_trace_gemm_tensor_cores(G, Or, cuda_device):
+    """n = 64: the trace GEMM runs as int8 digit GEMMs on the tensor cores (trace_tc.cu, both digit counts of the
+    native moduli); bit-exact against the oracle's loops, extreme residues (0, q-1) included."""
+    S, g = G
+    rng = np.random.default_rng(44)
+    batch = 3
+    mods = Or.moduli.reshape(1, -1, 1)
+    mats = [(rng.integers(0, 2 ** 63, size=(batch, Or.L, Or.n2), dtype=np.uint64) % mods) for _ in range(4)]
+    for m_ in mats:
+        m_[0, :, :64] = 0
+        m_[1, :, :128] = (mods - 1)[0]
+    mats = [m_.reshape(-1) for m_ in mats]
+    d = [dev(m_, cuda_device) for m_ in mats]
+    bpr, bpi = g.map_B_to_Bprime(d[2], d[3], batch)
+    obr, obi = Or.trace_map(mats[2], mats[3], batch)
+    assert (host(bpr) == obr).all() and (host(bpi) == obi).all()
+    cr, ci = g.trace_gemm(d[0], d[1], bpr, bpi, batch)
+    ocr, oci = Or.trace_gemm(mats[0], mats[1], obr, obi, batch)
+    assert (host(cr) == ocr).all() and (host(ci) == oci).all()
+
+
 def test_native_reference_drivers(G, cuda_device):
     import torch
     S, g = G
