@@ -438,7 +438,7 @@ extern "C" int mfhe_decode_lane_from_rns_eval(mfhe_ctx* c, const uint64_t* re, c
 // ---- samplers, keys -------------------------------------------------------------------------------------
 static int sample(mfhe_ctx* c, int kind, uint64_t* out, void* s, const char* who) {
     if (!c || !out) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
-    return done(sample_launch(kind, (u64*)out, c->d_moduli, c->n, c->L, c->phi, S(s)), who);
+    return done(sample_launch(kind, (u64*)out, c->d_moduli, c->d_mu, c->n, c->L, c->phi, S(s)), who);
 }
 extern "C" int mfhe_sample_uniform(mfhe_ctx* c, uint64_t* out, void* s) { return sample(c, 0, out, s, "sample_uniform"); }
 extern "C" int mfhe_sample_gaussian(mfhe_ctx* c, uint64_t* out, void* s) { return sample(c, 1, out, s, "sample_gaussian"); }
@@ -450,7 +450,7 @@ extern "C" int mfhe_keygen(mfhe_ctx* c, uint64_t* sk, void* s) {
     const size_t total = (size_t)c->phi * c->L * c->n;
     u64* sc = (u64*)c->take(total * 8);
     if (!sc) return fail(MFHE_ENOMEM, "keygen: arena too small");
-    cudaError_t e = sample_launch(2, sc, c->d_moduli, c->n, c->L, c->phi, S(s));
+    cudaError_t e = sample_launch(2, sc, c->d_moduli, c->d_mu, c->n, c->L, c->phi, S(s));
     if (e == cudaSuccess) {
         WcrtArgs a = wcrt_args(c, false);
         a.in = sc; a.out = (u64*)sk; a.cols = c->n;

@@ -132,7 +132,7 @@ struct RowArgs {                 // one launch over all phi*L*n rows of n coeffi
 };
 struct SmallTables;
 cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulonglong2* mu, cudaStream_t st);
-cudaError_t sample_launch(int kind, u64* out, const u64* moduli, int n, int limbs, int phi, cudaStream_t st);
+cudaError_t sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi, cudaStream_t st);
 cudaError_t layout_launch(const u64* in, u64* out, int n, int limbs, int phi, int in_layout, int out_layout, cudaStream_t st);
 cudaError_t ct_add_launch(const u64* c1, const u64* c2, u64* res, const u64* moduli, size_t T, int n, int limbs,
                           int ref_index, cudaStream_t st);

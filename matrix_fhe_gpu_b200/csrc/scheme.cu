@@ -110,7 +110,8 @@ __device__ __forceinline__ u64 splitmix64_s(u64 x) {
     return x ^ (x >> 31);
 }
 template <int KIND>
-__global__ void sample_kernel(u64* __restrict__ out, const u64* __restrict__ moduli, int n, int limbs, size_t total) {
+__global__ void sample_kernel(u64* __restrict__ out, const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu,
+                              int n, int limbs, size_t total) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     if (KIND == 2) {                                   // ternary, [w][limb][x]
@@ -120,28 +121,31 @@ __global__ void sample_kernel(u64* __restrict__ out, const u64* __restrict__ mod
         out[idx] = r == 0 ? 0 : r == 1 ? 1 : moduli[limb] - 1;
         return;
     }
-    const size_t n2 = (size_t)n * n, per = (size_t)limbs * n2, off = idx % per, limb = off / n2;
-    const u64 q = moduli[limb];
-    if (KIND == 0) {
+    const size_t n2 = (size_t)n * n, per = (size_t)limbs * n2;
+    if (KIND == 0) {                                   // LCG of the flat index, reduced with Barrett (== seed % q)
+        const size_t limb = (idx % per) / n2;
         u64 seed = 123456789ULL + idx;
         seed = seed * 6364136223846793005ULL + 1442695040888963407ULL;
-        out[idx] = seed % q;
+        out[idx] = reduce64(seed, moduli[limb], mu[limb].y);
     } else {
-        const u64 coeff_id = (u64)((idx / per) * n2 + off % n2);
-        const u64 r1 = splitmix64_s(0xD6E8FEB86659FD93ULL ^ coeff_id), r2 = splitmix64_s(r1);
+        // gaussian: idx runs over the LOGICAL coefficients [w][pos]; the value is drawn once (two fp64 transcendentals)
+        // and written to every limb, instead of being recomputed per limb
+        const size_t w = idx / n2, pos = idx - w * n2;
+        const u64 r1 = splitmix64_s(0xD6E8FEB86659FD93ULL ^ (u64)idx), r2 = splitmix64_s(r1);
         const double inv53 = 1.0 / 9007199254740992.0;
         const double u1 = ((double)(r1 >> 11) + 1.0) * inv53, u2 = ((double)(r2 >> 11) + 1.0) * inv53;
         const double mag = 3.2 * sqrt(-2.0 * log(u1));
         const long long z = llround(mag * cos(6.283185307179586 * u2));
-        out[idx] = z >= 0 ? (u64)z : q - (u64)(-z);
+        for (int limb = 0; limb < limbs; ++limb)
+            out[w * per + (size_t)limb * n2 + pos] = z >= 0 ? (u64)z : moduli[limb] - (u64)(-z);
     }
 }
-cudaError_t sample_launch(int kind, u64* out, const u64* moduli, int n, int limbs, int phi, cudaStream_t st) {
-    const size_t total = kind == 2 ? (size_t)phi * limbs * n : (size_t)phi * limbs * n * n;
+cudaError_t sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi, cudaStream_t st) {
+    const size_t total = kind == 2 ? (size_t)phi * limbs * n : kind == 1 ? (size_t)phi * n * n : (size_t)phi * limbs * n * n;
     const unsigned grid = (unsigned)((total + 255) / 256);
-    if (kind == 0) sample_kernel<0><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
-    else if (kind == 1) sample_kernel<1><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
-    else sample_kernel<2><<<grid, 256, 0, st>>>(out, moduli, n, limbs, total);
+    if (kind == 0) sample_kernel<0><<<grid, 256, 0, st>>>(out, moduli, mu, n, limbs, total);
+    else if (kind == 1) sample_kernel<1><<<grid, 256, 0, st>>>(out, moduli, mu, n, limbs, total);
+    else sample_kernel<2><<<grid, 256, 0, st>>>(out, moduli, mu, n, limbs, total);
     return cudaGetLastError();
 }
 
@@ -189,9 +193,18 @@ __global__ void ct_mul_kernel(const u64* __restrict__ c1, const u64* __restrict_
     const int l = ct_limb(idx, n, limbs, ref_index);
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
     const u64 b1 = c1[idx], a1 = c1[T + idx], b2 = c2[idx], a2 = c2[T + idx];
-    d0[idx] = mul_barrett(b1, b2, q, mu.x, mu.y);
-    d1[idx] = add_mod(mul_barrett(b1, a2, q, mu.x, mu.y), mul_barrett(a1, b2, q, mu.x, mu.y), q);
-    d2[idx] = mul_barrett(a1, a2, q, mu.x, mu.y);
+    if ((b1 | a1 | b2 | a2) < q || (b1 < q && a1 < q && b2 < q && a2 < q)) {
+        const barrett1_t bc = make_barrett1(q, mu.x, mu.y);    // canonical operands: the one-word Barrett is exact
+        d0[idx] = mul_barrett1(b1, b2, bc);
+        d1[idx] = add_mod(mul_barrett1(b1, a2, bc), mul_barrett1(a1, b2, bc), q);
+        d2[idx] = mul_barrett1(a1, a2, bc);
+    } else {
+        // reference_indexing picks the modulus by the POLY formula whatever the layout, so an operand may belong to a
+        // wider limb than q: full 128-bit Barrett (the reference's u128 % accepts any operands)
+        d0[idx] = mul_barrett(b1, b2, q, mu.x, mu.y);
+        d1[idx] = add_mod(mul_barrett(b1, a2, q, mu.x, mu.y), mul_barrett(a1, b2, q, mu.x, mu.y), q);
+        d2[idx] = mul_barrett(a1, a2, q, mu.x, mu.y);
+    }
 }
 cudaError_t ct_mul_launch(const u64* c1, const u64* c2, u64* d0, u64* d1, u64* d2, const u64* moduli, const ulonglong2* mu,
                           size_t T, int n, int limbs, int ref_index, cudaStream_t st) {
@@ -282,8 +295,14 @@ __global__ void trace_rescale_kernel(u64* __restrict__ Cr, u64* __restrict__ Ci,
     const int l = (int)((idx / ((size_t)n * n)) % limbs);
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
     const u64 inv = l == 0 ? inv0 : l == 1 ? inv1 : l == 2 ? inv2 : 0;
-    Cr[idx] = mul_barrett(Cr[idx], inv, q, mu.x, mu.y);
-    Ci[idx] = mul_barrett(Ci[idx], inv, q, mu.x, mu.y);
+    if (inv < q && Cr[idx] < q && Ci[idx] < q) {               // canonical operands: one-word Barrett
+        const barrett1_t bc = make_barrett1(q, mu.x, mu.y);
+        Cr[idx] = mul_barrett1(Cr[idx], inv, bc);
+        Ci[idx] = mul_barrett1(Ci[idx], inv, bc);
+    } else {
+        Cr[idx] = mul_barrett(Cr[idx], inv, q, mu.x, mu.y);
+        Ci[idx] = mul_barrett(Ci[idx], inv, q, mu.x, mu.y);
+    }
 }
 cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                  u64 inv0, u64 inv1, u64 inv2, cudaStream_t st) {
