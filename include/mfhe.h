@@ -264,6 +264,16 @@ int mfhe_bconv(const mfhe_bconv_plan *plan, const uint64_t *d_in, uint64_t *d_ou
  * partials mod p_j (mfhe_bconv_reduce after an all-gather / reduce-scatter) equals mfhe_bconv. */
 int mfhe_bconv_partial(const mfhe_bconv_plan *plan, const uint64_t *d_in_local, int in_start, int in_count,
                        uint64_t *d_partial, size_t N, size_t batch, void *stream);
+/* fused partial + exchange: the same sums as mfhe_bconv_partial, but output limb j of batch item b is
+ * stored at dst[j] + b * dst_batch_stride[j] (words; dst / dst_batch_stride are HOST arrays of l_out
+ * entries, passed to the kernel by value).  dst[j] may point into a PEER GPU's memory (NVLink P2P /
+ * CUDA symmetric memory): the kernel then writes every partial sum straight into the receive buffer of
+ * the rank that owns output limb j -- layout [src_rank][batch][out_count][N] there, which is what
+ * mfhe_bconv_reduce consumes -- so the exchange of ph/src/rns_bconv.cu:212-229's cross-limb sum rides
+ * on the compute kernel's stores and no collective follows (the caller orders steps with a barrier). */
+int mfhe_bconv_partial_scatter(const mfhe_bconv_plan *plan, const uint64_t *d_in_local, int in_start, int in_count,
+                               uint64_t *const *dst, const size_t *dst_batch_stride, size_t N, size_t batch,
+                               void *stream);
 /* d_parts [nparts][batch][out_count][N] -> d_out [batch][out_count][N], output limbs
  * [out_start, out_start+out_count) */
 int mfhe_bconv_reduce(const mfhe_bconv_plan *plan, const uint64_t *d_parts, int nparts, int out_start, int out_count,

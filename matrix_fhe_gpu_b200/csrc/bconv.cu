@@ -32,11 +32,17 @@ struct mfhe_bconv_plan {
 
 namespace {
 constexpr int BC = 128;    // coefficients per CTA
+constexpr int kScatterMax = 128;
 
+// Destination table of the fused partial + exchange form (passed by value, 3 KiB of kernel parameters):
+// output limb j of batch item b goes to base[j] + b * bstride[j]; base[j] may be a peer GPU's memory.
+struct BconvScatter { u64* base[kScatterMax]; size_t bstride[kScatterMax]; };
+
+template <bool SC>
 __global__ void __launch_bounds__(BC)
 bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_in_total, int in_start, int in_count,
              int l_out, const u64* __restrict__ q, const tw_t* __restrict__ qhat_inv, const u64* __restrict__ qhat_mod_p,
-             const u64* __restrict__ p, const ulonglong2* __restrict__ mu_p) {
+             const u64* __restrict__ p, const ulonglong2* __restrict__ mu_p, const __grid_constant__ BconvScatter sc) {
     extern __shared__ u64 sy[];        // [in_count][BC]
     const size_t d = (size_t)blockIdx.x * BC + threadIdx.x;
     const size_t b = blockIdx.y;
@@ -48,7 +54,7 @@ bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_
     }
     // each thread reads back only its own column: no barrier needed
     if (!live) return;
-    u64* o = out + b * (size_t)l_out * N;
+    u64* o = SC ? nullptr : out + b * (size_t)l_out * N;
     for (int j = 0; j < l_out; ++j) {
         u64 lo = 0, hi = 0;
         const u64* w = qhat_mod_p + (size_t)j * l_in_total + in_start;
@@ -58,7 +64,9 @@ bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_
             lo += pl; hi += ph + (lo < pl);
         }
         const ulonglong2 m = mu_p[j];
-        o[(size_t)j * N + d] = reduce128(lo, hi, p[j], m.x, m.y);
+        const u64 r = reduce128(lo, hi, p[j], m.x, m.y);
+        if constexpr (SC) sc.base[j][b * sc.bstride[j] + d] = r;
+        else              o[(size_t)j * N + d] = r;
     }
 }
 
@@ -130,21 +138,28 @@ extern "C" int mfhe_bconv_plan_create(int l_in, const uint64_t* q_in, int l_out,
 }
 
 static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start, int in_count, uint64_t* out, size_t N,
-                     size_t batch, void* stream, const char* who) {
-    if (!b || !in || !out) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
+                     size_t batch, void* stream, const char* who, const BconvScatter* sc = nullptr) {
+    if (!b || !in || (!out && !sc)) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
     if (in_start < 0 || in_count < 1 || in_start + in_count > b->l_in) return fail(MFHE_EINVAL, std::string(who) + ": limb window out of range");
     if (!N || !batch) return MFHE_OK;
     if (batch > 65535) return fail(MFHE_EINVAL, std::string(who) + ": batch too large");
     const size_t smem = (size_t)in_count * BC * 8;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(bconv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(bconv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(bconv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, who);
         attr_set = true;
     }
     dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
-    bconv_kernel<<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out,
-                                                          b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p);
+    if (sc) {
+        bconv_kernel<true><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, nullptr, N, b->l_in, in_start, in_count, b->l_out,
+                                                                    b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p, *sc);
+    } else {
+        static const BconvScatter none{};
+        bconv_kernel<false><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out,
+                                                                     b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p, none);
+    }
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
 }
@@ -154,6 +169,17 @@ extern "C" int mfhe_bconv(const mfhe_bconv_plan* b, const uint64_t* in, uint64_t
 extern "C" int mfhe_bconv_partial(const mfhe_bconv_plan* b, const uint64_t* in, int in_start, int in_count, uint64_t* out,
                                   size_t N, size_t batch, void* s) {
     return bconv_run(b, in, in_start, in_count, out, N, batch, s, "bconv_partial");
+}
+extern "C" int mfhe_bconv_partial_scatter(const mfhe_bconv_plan* b, const uint64_t* in, int in_start, int in_count,
+                                          uint64_t* const* dst, const size_t* dst_batch_stride, size_t N, size_t batch, void* s) {
+    if (!b || !dst || !dst_batch_stride) return fail(MFHE_EINVAL, "bconv_partial_scatter: NULL argument");
+    if (b->l_out > kScatterMax) return fail(MFHE_EUNSUPPORTED, "bconv_partial_scatter: more than 128 output limbs");
+    BconvScatter sc{};
+    for (int j = 0; j < b->l_out; ++j) {
+        if (!dst[j]) return fail(MFHE_EINVAL, "bconv_partial_scatter: NULL destination");
+        sc.base[j] = (u64*)dst[j]; sc.bstride[j] = dst_batch_stride[j];
+    }
+    return bconv_run(b, in, in_start, in_count, nullptr, N, batch, s, "bconv_partial_scatter", &sc);
 }
 extern "C" int mfhe_bconv_reduce(const mfhe_bconv_plan* b, const uint64_t* parts, int nparts, int out_start, int out_count,
                                  uint64_t* out, size_t N, size_t batch, void* s) {

@@ -76,6 +76,7 @@ def _L():
         "mfhe_bconv_plan_create": [_ci, C.POINTER(_u64), _ci, C.POINTER(_u64), C.POINTER(_vp)],
         "mfhe_bconv": [_vp, _vp, _vp, C.c_size_t, C.c_size_t, _vp],
         "mfhe_bconv_partial": [_vp, _vp, _ci, _ci, _vp, C.c_size_t, C.c_size_t, _vp],
+        "mfhe_bconv_partial_scatter": [_vp, _vp, _ci, _ci, C.POINTER(_vp), C.POINTER(C.c_size_t), C.c_size_t, C.c_size_t, _vp],
         "mfhe_bconv_reduce": [_vp, _vp, _ci, _ci, _ci, _vp, C.c_size_t, C.c_size_t, _vp],
     }
     for name, args in sig.items():
@@ -411,6 +412,15 @@ class BconvPlan:
         o = torch.empty(batch * len(self.p) * N, dtype=torch.int64, device=x_local.device)
         check(_L().mfhe_bconv_partial(self._h, _dev_ptr(x_local), in_start, in_count, _dev_ptr(o), N, batch, _stream_handle()))
         return o
+
+    def partial_scatter(self, x_local, in_start, in_count, dst_ptrs, dst_batch_strides, N, batch=1):
+        """mfhe_bconv_partial_scatter: output limb j of item b is stored at dst_ptrs[j] + b * dst_batch_strides[j]
+        words; dst_ptrs are raw device addresses (own or peer memory), one per output limb."""
+        if len(dst_ptrs) != len(self.p) or len(dst_batch_strides) != len(self.p):
+            raise ValueError("partial_scatter: one destination and stride per output limb")
+        pa = (_vp * len(self.p))(*[_vp(int(v)) for v in dst_ptrs])
+        sa = (C.c_size_t * len(self.p))(*[int(v) for v in dst_batch_strides])
+        check(_L().mfhe_bconv_partial_scatter(self._h, _dev_ptr(x_local), in_start, in_count, pa, sa, N, batch, _stream_handle()))
 
     def reduce(self, parts, nparts, out_start, out_count, N, batch=1):
         import torch

@@ -15,7 +15,17 @@ Two cases exist on this path:
   nwt_2d_radix8_backward/forward_inplace on a limb window (ph/src/ntt/intt_2d.cu:724-757,
   fntt_2d.cu:620-653); the conversion is DBaseConverter::bConv_BEHZ (ph/src/rns_bconv.cu:212-229).
 
-`limb_windows`, `batch_slice` and `exchange_partials` are pure torch / torch.distributed (they run on
+Three forms of the exchange exist (`tools/run_sharded.py --exchange`):
+  nccl       partial -> pack -> one all-to-all (NCCL) -> reduce                      (`step`)
+  pipelined  the same per batch group, the all-to-all of group g overlapping the INTT + partial sums of
+             group g+1 and the reduce + NTT of group g-1                             (`step_pipelined`)
+  p2p        FUSED compute + exchange: mfhe_bconv_partial_scatter stores every partial sum straight into
+             the receive buffer of the rank that owns the output limb (CUDA symmetric memory over NVLink /
+             NVSwitch peer mappings, `scatter_table` gives the destination of each output limb), so there is
+             no pack pass, no send buffer and no collective -- one device-side barrier orders the step
+             (`step_p2p`; double-buffered so that step k+1's stores never meet step k's reads).
+
+`limb_windows`, `batch_slice`, `scatter_table` and `exchange_partials` are pure torch / torch.distributed (they run on
 CPU tensors over gloo in the test-suite and on CUDA tensors over NCCL on the box); the compute calls
 go through the C ABI and need the GPU.
 """
@@ -71,6 +81,22 @@ def exchange_partials(partial, out_windows: Sequence[Tuple[int, int]], rank: int
     return recv.view(world, batch, mine, n)
 
 
+def scatter_table(peer_bases: Sequence[int], out_windows: Sequence[Tuple[int, int]], src_rank: int, batch: int, n: int,
+                  count_max: int | None = None):
+    """Destinations for mfhe_bconv_partial_scatter on rank `src_rank`.
+
+    Every rank r owns a receive buffer (base address peer_bases[r], as seen from src_rank) laid out
+    [world][batch][count_r][N] u64 -- slot `src_rank` of it is ours -- where count_r is rank r's output window.
+    Returns (ptrs, batch_strides_in_words), one entry per output limb j: item b of limb j goes to
+    ptrs[j] + 8 * (b * strides[j] + coefficient)."""
+    ptrs, strides = [], []
+    for r, (s, c) in enumerate(out_windows):
+        for j in range(s, s + c):
+            ptrs.append(int(peer_bases[r]) + 8 * ((src_rank * batch * c + (j - s)) * n))
+            strides.append(c * n)
+    return ptrs, strides
+
+
 def emulate_exchange(partials, out_windows: Sequence[Tuple[int, int]], rank: int):
     """Single-process stand-in for exchange_partials: partials[r] is rank r's [batch][L_out][N]."""
     import torch
@@ -109,4 +135,76 @@ class LimbShardedBconv:
     def step(self, x_local, batch: int):
         partial = self.local_partial(x_local, batch)
         parts = exchange_partials(partial, self.p_windows, self.rank, self.world, self.group)
+        return self.finish(parts, batch)
+
+    # ---- pipelined NCCL form ------------------------------------------------------------------------
+    def step_pipelined(self, x_local, batch: int, groups: int = 4):
+        """Same result as `step`, the batch cut into `groups` slices: while NCCL moves slice g (on its own
+        stream, async_op) the compute stream already runs INTT + partial sums of slice g+1 and, one slice
+        later, reduce + NTT of slice g."""
+        import torch
+        import torch.distributed as dist
+        groups = max(1, min(groups, batch))
+        bounds = [batch * g // groups for g in range(groups + 1)]
+        mine = self.p_windows[self.rank][1]
+        x = x_local.view(batch, -1, self.n)
+        out = torch.empty(batch, mine, self.n, dtype=x_local.dtype, device=x_local.device)
+        inflight = []            # (work, recv, send, b0, nb)
+
+        def drain():
+            work, recv, send, b0, nb = inflight.pop(0)
+            if work is not None:
+                work.wait()                                     # compute stream waits for NCCL's stream
+            out[b0:b0 + nb] = self.finish(recv.view(self.world, nb, mine, self.n), nb)
+
+        for g in range(groups):
+            b0, nb = bounds[g], bounds[g + 1] - bounds[g]
+            if nb == 0:
+                continue
+            partial = self.local_partial(x[b0:b0 + nb], nb)
+            send, in_splits = pack_for_exchange(partial, self.p_windows)
+            recv = torch.empty(self.world * nb * mine * self.n, dtype=send.dtype, device=send.device)
+            if self.world == 1:
+                recv.copy_(send); work = None
+            else:
+                work = dist.all_to_all_single(recv, send, output_split_sizes=[nb * mine * self.n] * self.world,
+                                              input_split_sizes=in_splits, group=self.group, async_op=True)
+            inflight.append((work, recv, send, b0, nb))
+            if len(inflight) > 1:
+                drain()
+        while inflight:
+            drain()
+        return out
+
+    # ---- fused compute + exchange over peer memory -----------------------------------------------------
+    def enable_p2p(self, batch: int):
+        """Allocates the double-buffered symmetric receive buffers ([world][batch][count][N] each) and exchanges
+        their peer addresses.  Needs an initialised NCCL process group with all ranks on one NVLink domain."""
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        dev = torch.device("cuda", torch.cuda.current_device())
+        cmax = max(c for _, c in self.p_windows)
+        words = self.world * batch * cmax * self.n
+        grp = self.group if self.group is not None else dist.group.WORLD
+        self._p2p = []
+        for _ in range(2):
+            buf = symm.empty(words, dtype=torch.int64, device=dev)
+            hdl = symm.rendezvous(buf, grp)
+            ptrs, strides = scatter_table([int(v) for v in hdl.buffer_ptrs], self.p_windows, self.rank, batch, self.n)
+            self._p2p.append((buf, hdl, ptrs, strides))
+        self._p2p_batch, self._p2p_phase = batch, 0
+
+    def step_p2p(self, x_local, batch: int):
+        """INTT -> partial sums stored directly into the owners' receive buffers -> device barrier -> reduce -> NTT."""
+        if getattr(self, "_p2p", None) is None or self._p2p_batch != batch:
+            raise RuntimeError("step_p2p: call enable_p2p(batch) first")
+        buf, hdl, ptrs, strides = self._p2p[self._p2p_phase]
+        self._p2p_phase ^= 1
+        qs, qc = self.q_windows[self.rank]
+        mine = self.p_windows[self.rank][1]
+        self.plan_q.inverse_limbs_(x_local, qs, qc)
+        self.bconv.partial_scatter(x_local, qs, qc, ptrs, strides, self.n, batch)
+        hdl.barrier(channel=0)          # stream-ordered: every rank's stores are complete and visible after it
+        parts = buf[: self.world * batch * mine * self.n].view(self.world, batch, mine, self.n)
         return self.finish(parts, batch)

@@ -117,3 +117,32 @@ def test_emulate_exchange_matches_pack():
         assert splits == [batch * cc * N for _, cc in win]
         off = sum(splits[:r])
         assert torch.equal(send[off:off + splits[r]].view(batch, c, N), partials[r][:, s:s + c, :])
+
+
+@pytest.mark.parametrize("l_out,world,batch,n", [(16, 8, 3, 8), (5, 2, 2, 4), (7, 4, 1, 16)])
+def test_scatter_table_addresses_receive_layout(l_out, world, batch, n):
+    """scatter_table must address slot [src][b][j - start][coeff] of the owner's [world][batch][count][N] buffer:
+    writing partials through the table into numpy stand-ins of the peer buffers gives exactly emulate_exchange."""
+    import torch
+    wins = S.limb_windows(l_out, world)
+    cmax = max(c for _, c in wins)
+    words = world * batch * cmax * n
+    bases = [r * words * 8 + 4096 for r in range(world)]            # fake, disjoint "peer addresses"
+    mem = {r: np.full(words, -1, dtype=np.int64) for r in range(world)}
+    rng = np.random.default_rng(3)
+    partials = [rng.integers(0, 1 << 60, size=(batch, l_out, n), dtype=np.int64) for _ in range(world)]
+    for src in range(world):
+        ptrs, strides = S.scatter_table(bases, wins, src, batch, n)
+        assert len(ptrs) == l_out and len(strides) == l_out
+        for j in range(l_out):
+            owner = next(r for r, (s, c) in enumerate(wins) if s <= j < s + c)
+            off = (ptrs[j] - bases[owner]) // 8
+            assert (ptrs[j] - bases[owner]) % 8 == 0 and 0 <= off
+            for b in range(batch):
+                lo = off + b * strides[j]
+                assert lo + n <= words
+                mem[owner][lo:lo + n] = partials[src][b, j]
+    for r, (s, c) in enumerate(wins):
+        want = S.emulate_exchange([torch.from_numpy(p) for p in partials], wins, r).numpy()
+        got = mem[r][: world * batch * c * n].reshape(world, batch, c, n)
+        assert (got == want).all()

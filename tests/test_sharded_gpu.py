@@ -51,13 +51,45 @@ def test_limb_sharded_step_emulated(cuda_device, logn, l_in, l_out, bits, world,
         assert (got == want[:, s:s + c]).all()
 
 
-def test_limb_sharded_step_nccl():
+@pytest.mark.parametrize("logn,l_in,l_out,bits,world,batch", [(12, 6, 4, 55, 4, 2), (12, 5, 3, 60, 2, 3)])
+def test_partial_scatter_matches_partial_plus_exchange(cuda_device, logn, l_in, l_out, bits, world, batch):
+    """mfhe_bconv_partial_scatter (fused partial + exchange) against mfhe_bconv_partial followed by the exchange:
+    the 'peer' receive buffers are plain local tensors here; under torchrun they are symmetric-memory peers."""
+    import torch
+    from matrix_fhe_gpu_b200 import sharded as S
+    N = 1 << logn
+    primes = [int(v) for v in O.get_primes(N, bits, l_in + l_out)]
+    q, p = primes[:l_in], primes[l_in:]
+    x = O.synth_polys(5, batch, q, N)
+    ranks = [S.LimbShardedBconv(logn, q, p, r, world) for r in range(world)]
+    wins = ranks[0].p_windows
+    cmax = max(c for _, c in wins)
+    bufs = [torch.full((world * batch * cmax * N,), -1, dtype=torch.int64, device=cuda_device) for _ in range(world)]
+    bases = [b.data_ptr() for b in bufs]
+    partials = []
+    for r, sh in enumerate(ranks):
+        s, c = sh.q_windows[r]
+        xl = torch.from_numpy(np.ascontiguousarray(x[:, s:s + c]).view(np.int64)).to(cuda_device)
+        sh.plan_q.inverse_limbs_(xl, s, c)
+        partials.append(sh.bconv.partial(xl, s, c, N, batch).view(batch, l_out, N))
+        ptrs, strides = S.scatter_table(bases, wins, r, batch, N)
+        sh.bconv.partial_scatter(xl, s, c, ptrs, strides, N, batch)
+    torch.cuda.synchronize()
+    for r, (s, c) in enumerate(wins):
+        want = S.emulate_exchange(partials, wins, r)
+        got = bufs[r][: world * batch * c * N].view(world, batch, c, N)
+        assert torch.equal(got, want)
+        assert bool((bufs[r][world * batch * c * N:] == -1).all())         # nothing written past the window
+
+
+@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p"])
+def test_limb_sharded_step_nccl(exchange):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", "29631", os.path.join(ROOT, "tools", "run_sharded.py"), "--logn", "13", "--lin", "6", "--lout", "4",
-           "--batch", "2", "--check", "--steps", "2"]
+           "--batch", "3" if exchange == "pipelined" else "2", "--check", "--steps", "3", "--exchange", exchange]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "parity ok" in r.stdout

@@ -29,6 +29,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--exchange", choices=["nccl", "pipelined", "p2p"], default="nccl",
+                    help="nccl: one all-to-all; pipelined: per batch group, overlapped; p2p: fused partial + peer stores")
+    ap.add_argument("--groups", type=int, default=4)
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -59,8 +62,17 @@ def main():
     x0 = torch.from_numpy(x_loc.view(np.int64)).to(dev)
     work = torch.empty_like(x0)
 
+    if a.exchange == "p2p":
+        if world < 2:
+            raise SystemExit("--exchange p2p needs torchrun with >= 2 ranks")
+        sh.enable_p2p(a.batch)
+
     def step():
         work.copy_(x0)
+        if a.exchange == "p2p":
+            return sh.step_p2p(work, a.batch)
+        if a.exchange == "pipelined":
+            return sh.step_pipelined(work, a.batch, a.groups)
         return sh.step(work, a.batch)
 
     out = None
@@ -94,7 +106,9 @@ def main():
         print(json.dumps({"metric": "limb_sharded_intt_bconv_ntt_polys_per_s", "value": a.batch / (ms * 1e-3), "unit": "polys/s",
                           "n_gpus": world, "ms_per_step": ms, "config": {"N": N, "L_in": a.lin, "L_out": a.lout, "bits": a.bits,
                                                                          "batch": a.batch},
-                          "exchange": {"kind": "all_to_all of partial sums (NCCL)", "bytes_sent_per_rank": sent,
+                          "exchange": {"kind": {"nccl": "all_to_all of partial sums (NCCL)",
+                                                "pipelined": "all_to_all per batch group (NCCL, async) overlapped with the transforms, groups=%d" % a.groups,
+                                                "p2p": "partial sums stored by the bconv kernel into the owners' symmetric-memory buffers over NVLink, one device barrier"}[a.exchange], "bytes_sent_per_rank": sent,
                                        "note": "GB/s below is an upper bound on link use: whole step time, not the collective alone",
                                        "gbs_per_rank_over_step": sent / (ms * 1e-3) / 1e9},
                           "parity": ("ok" if ok else "FAILED") if a.check else "not checked"}))
