@@ -195,16 +195,40 @@ class LimbShardedBconv:
             self._p2p.append((buf, hdl, ptrs, strides))
         self._p2p_batch, self._p2p_phase = batch, 0
 
-    def step_p2p(self, x_local, batch: int):
-        """INTT -> partial sums stored directly into the owners' receive buffers -> device barrier -> reduce -> NTT."""
+    def step_p2p(self, x_local, batch: int, groups: int = 1):
+        """INTT -> partial sums stored directly into the owners' receive buffers -> device barrier -> reduce -> NTT.
+
+        groups > 1 cuts the batch into slices that alternate between two side streams, so that the NVLink-bound
+        scatter kernel of one slice runs next to the integer-bound INTT of the following one."""
+        import torch
         if getattr(self, "_p2p", None) is None or self._p2p_batch != batch:
             raise RuntimeError("step_p2p: call enable_p2p(batch) first")
         buf, hdl, ptrs, strides = self._p2p[self._p2p_phase]
         self._p2p_phase ^= 1
         qs, qc = self.q_windows[self.rank]
         mine = self.p_windows[self.rank][1]
-        self.plan_q.inverse_limbs_(x_local, qs, qc)
-        self.bconv.partial_scatter(x_local, qs, qc, ptrs, strides, self.n, batch)
+        groups = max(1, min(groups, batch))
+        if groups == 1:
+            self.plan_q.inverse_limbs_(x_local, qs, qc)
+            self.bconv.partial_scatter(x_local, qs, qc, ptrs, strides, self.n, batch)
+        else:
+            if getattr(self, "_side", None) is None:
+                self._side = [torch.cuda.Stream(), torch.cuda.Stream()]
+            cur = torch.cuda.current_stream()
+            x = x_local.view(batch, qc, self.n)
+            for g in range(groups):
+                b0, b1 = batch * g // groups, batch * (g + 1) // groups
+                if b1 == b0:
+                    continue
+                st = self._side[g & 1]
+                st.wait_stream(cur)
+                with torch.cuda.stream(st):
+                    xs = x[b0:b1]
+                    self.plan_q.inverse_limbs_(xs, qs, qc)
+                    self.bconv.partial_scatter(xs, qs, qc, [p + 8 * b0 * sj for p, sj in zip(ptrs, strides)], strides,
+                                               self.n, b1 - b0)
+            for st in self._side:
+                cur.wait_stream(st)
         hdl.barrier(channel=0)          # stream-ordered: every rank's stores are complete and visible after it
         parts = buf[: self.world * batch * mine * self.n].view(self.world, batch, mine, self.n)
         return self.finish(parts, batch)

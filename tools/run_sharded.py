@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--exchange", choices=["nccl", "pipelined", "p2p"], default="nccl",
                     help="nccl: one all-to-all; pipelined: per batch group, overlapped; p2p: fused partial + peer stores")
     ap.add_argument("--groups", type=int, default=4)
+    ap.add_argument("--p2p-groups", type=int, default=1, help="p2p: batch slices alternating between two streams")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -70,7 +71,7 @@ def main():
     def step():
         work.copy_(x0)
         if a.exchange == "p2p":
-            return sh.step_p2p(work, a.batch)
+            return sh.step_p2p(work, a.batch, a.p2p_groups)
         if a.exchange == "pipelined":
             return sh.step_pipelined(work, a.batch, a.groups)
         return sh.step(work, a.batch)
@@ -108,7 +109,7 @@ def main():
                                                                          "batch": a.batch},
                           "exchange": {"kind": {"nccl": "all_to_all of partial sums (NCCL)",
                                                 "pipelined": "all_to_all per batch group (NCCL, async) overlapped with the transforms, groups=%d" % a.groups,
-                                                "p2p": "partial sums stored by the bconv kernel into the owners' symmetric-memory buffers over NVLink, one device barrier"}[a.exchange], "bytes_sent_per_rank": sent,
+                                                "p2p": "partial sums stored by the bconv kernel into the owners' symmetric-memory buffers over NVLink, one device barrier, stream groups=%d" % a.p2p_groups}[a.exchange], "bytes_sent_per_rank": sent,
                                        "note": "GB/s below is an upper bound on link use: whole step time, not the collective alone",
                                        "gbs_per_rank_over_step": sent / (ms * 1e-3) / 1e9},
                           "parity": ("ok" if ok else "FAILED") if a.check else "not checked"}))
