@@ -10,6 +10,7 @@
 // mfhe_bconv_reduce adds the partials: this is the only step of the whole path that needs a
 // collective.
 #include <algorithm>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <vector>
@@ -38,7 +39,10 @@ constexpr int kScatterMax = 128;
 // output limb j of batch item b goes to base[j] + b * bstride[j]; base[j] may be a peer GPU's memory.
 struct BconvScatter { u64* base[kScatterMax]; size_t bstride[kScatterMax]; };
 
-template <bool SC>
+// W1: the accumulated sum is below 2^(k+61) (k = bits of p_j; host-checked: in_count * max q <= 2^61), so ONE-word
+// Barrett reduces it (same bound as mul_barrett1: qhat >= floor(v / p) - 2): one 64x64 high product instead of the
+// five wide products of reduce128.  At in_count = 6 (config 5 on 8 ranks) the reduction is as expensive as the sums.
+template <bool SC, bool W1>
 __global__ void __launch_bounds__(BC)
 bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_in_total, int in_start, int in_count,
              int l_out, const u64* __restrict__ q, const tw_t* __restrict__ qhat_inv, const u64* __restrict__ qhat_mod_p,
@@ -64,7 +68,15 @@ bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_
             lo += pl; hi += ph + (lo < pl);
         }
         const ulonglong2 m = mu_p[j];
-        const u64 r = reduce128(lo, hi, p[j], m.x, m.y);
+        u64 r;
+        if constexpr (W1) {
+            const barrett1_t bc = make_barrett1(p[j], m.x, m.y);
+            const u64 x1 = (lo >> bc.sh) | (hi << (64 - bc.sh));
+            r = lo - __umul64hi(x1, bc.mu1) * bc.q;
+            r = csub(csub(r, bc.q2), bc.q);
+        } else {
+            r = reduce128(lo, hi, p[j], m.x, m.y);
+        }
         if constexpr (SC) sc.base[j][b * sc.bstride[j] + d] = r;
         else              o[(size_t)j * N + d] = r;
     }
@@ -146,20 +158,29 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     const size_t smem = (size_t)in_count * BC * 8;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(bconv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(bconv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+        cudaError_t e = cudaSuccess;
+        const void* fns[4] = {(const void*)bconv_kernel<false, false>, (const void*)bconv_kernel<false, true>,
+                              (const void*)bconv_kernel<true, false>, (const void*)bconv_kernel<true, true>};
+        for (const void* f : fns)
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, who);
         attr_set = true;
     }
     dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
-    if (sc) {
-        bconv_kernel<true><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, nullptr, N, b->l_in, in_start, in_count, b->l_out,
-                                                                    b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p, *sc);
-    } else {
-        static const BconvScatter none{};
-        bconv_kernel<false><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out,
-                                                                     b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p, b->d_mu_p, none);
-    }
+    // one-word Barrett iff sum_i y_i c_i < in_count * qmax * p_j < 2^(k_j + 61) for every j: in_count * qmax <= 2^61
+    uint64_t qmax = 0;
+    for (int i = in_start; i < in_start + in_count; ++i) qmax = std::max(qmax, b->q[i]);
+    static const bool force128 = getenv("MFHE_BCONV_128") != nullptr;
+    const bool w1 = !force128 && (unsigned __int128)qmax * (unsigned)in_count <= ((unsigned __int128)1 << 61);
+    static const BconvScatter none{};
+    const BconvScatter& tab = sc ? *sc : none;
+#define MFHE_BCONV_LAUNCH(SCV, W1V)                                                                                        \
+    bconv_kernel<SCV, W1V><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, \
+                                                                    b->l_out, b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p,  \
+                                                                    b->d_mu_p, tab)
+    if (sc) { if (w1) MFHE_BCONV_LAUNCH(true, true); else MFHE_BCONV_LAUNCH(true, false); }
+    else    { if (w1) MFHE_BCONV_LAUNCH(false, true); else MFHE_BCONV_LAUNCH(false, false); }
+#undef MFHE_BCONV_LAUNCH
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
 }

@@ -411,6 +411,24 @@ def test_trace_and_glperm(S, cuda_device, name):
     assert (back == want2).all()
 
 
+@pytest.mark.parametrize("N,l_in,l_out,bits", [(1024, 8, 3, 58), (1024, 48, 4, 55), (1024, 9, 3, 58), (512, 2, 2, 60)])
+def test_bconv_extreme_residues_one_word_barrett(S, cuda_device, N, l_in, l_out, bits):
+    """The kernel reduces the accumulated 128-bit sum with a one-word Barrett whenever in_count * max q <= 2^61
+    (8 x 58-bit is the boundary case, 48 x 55-bit the unsharded config-5 shape; 9 x 58-bit and 2 x 60-bit... the
+    latter still qualifies, the former takes the 128-bit form).  Inputs at the extremes (all q_i - 1, all 0, random)
+    make the sums as large as they can get; every output must equal the oracle's."""
+    primes = [int(v) for v in O.get_primes(N, bits, l_in + l_out)]
+    q, p = primes[:l_in], primes[l_in:]
+    qa = np.array(q, dtype=np.uint64).reshape(-1, 1)
+    rng = np.random.default_rng(31)
+    x = np.stack([np.broadcast_to(qa - np.uint64(1), (l_in, N)), np.zeros((l_in, N), dtype=np.uint64),
+                  rng.integers(0, 2 ** 63, size=(l_in, N), dtype=np.uint64) % qa]).astype(np.uint64)
+    plan = S.BconvPlan(q, p)
+    got = host(plan.convert(dev(np.ascontiguousarray(x).reshape(-1), cuda_device), N, 3)).reshape(3, l_out, N)
+    for b in range(3):
+        assert (got[b] == O.bconv(x[b], q, p)).all()
+
+
 @pytest.mark.parametrize("N,l_in,l_out,bits,batch", [(4096, 6, 3, 55, 2), (8192, 12, 4, 60, 1), (1024, 3, 5, 36, 3)])
 def test_bconv_bit_exact(S, cuda_device, N, l_in, l_out, bits, batch):
     primes = [int(v) for v in O.get_primes(N, bits, l_in + l_out)]
