@@ -42,43 +42,101 @@ struct BconvScatter { u64* base[kScatterMax]; size_t bstride[kScatterMax]; };
 // W1: the accumulated sum is below 2^(k+61) (k = bits of p_j; host-checked: in_count * max q <= 2^61), so ONE-word
 // Barrett reduces it (same bound as mul_barrett1: qhat >= floor(v / p) - 2): one 64x64 high product instead of the
 // five wide products of reduce128.  At in_count = 6 (config 5 on 8 ranks) the reduction is as expensive as the sums.
-template <bool SC, bool W1>
+// IC > 0: in_count is the compile-time constant IC -- the y_i stay in registers (no shared memory), the sum over i is
+// fully unrolled and two output limbs are formed per trip, so the loop and address arithmetic that made the generic
+// form issue-bound (ncu: 4 200 instructions per coefficient for 96 multiply-accumulates, profiles/r1_21) disappears.
+// IC == 0: any in_count, y_i in shared memory.
+template <bool W1>
+__device__ __forceinline__ u64 bconv_fold(u64 lo, u64 hi, u64 pj, ulonglong2 m) {
+    if constexpr (W1) {
+        const barrett1_t bc = make_barrett1(pj, m.x, m.y);
+        const u64 x1 = (lo >> bc.sh) | (hi << (64 - bc.sh));
+        const u64 r = lo - __umul64hi(x1, bc.mu1) * bc.q;
+        return csub(csub(r, bc.q2), bc.q);
+    } else {
+        return reduce128(lo, hi, pj, m.x, m.y);
+    }
+}
+// (hi:lo) += y * c on 32-bit halves with explicit carry chains: four 32x32->64 multiply-adds (ptxas pairs each
+// mad.lo.cc / madc.hi into one IMAD.WIDE) + carry adds, instead of the separate low and high 64-bit products the
+// compiler emits for  y * c  and  __umul64hi(y, c)  (about 16 IMAD + 10 IADD3 per term).
+__device__ __forceinline__ void mac128(u64& lo, u64& hi, u64 y, u64 c) {
+    u32 a0 = (u32)lo, a1 = (u32)(lo >> 32), a2 = (u32)hi, a3 = (u32)(hi >> 32);
+    const u32 y0 = (u32)y, y1 = (u32)(y >> 32), c0 = (u32)c, c1 = (u32)(c >> 32);
+    asm("mad.lo.cc.u32 %0, %4, %6, %0;\n\t"
+        "madc.hi.cc.u32 %1, %4, %6, %1;\n\t"
+        "addc.cc.u32 %2, %2, 0;\n\t"
+        "addc.u32 %3, %3, 0;\n\t"
+        "mad.lo.cc.u32 %1, %4, %7, %1;\n\t"
+        "madc.hi.cc.u32 %2, %4, %7, %2;\n\t"
+        "addc.u32 %3, %3, 0;\n\t"
+        "mad.lo.cc.u32 %1, %5, %6, %1;\n\t"
+        "madc.hi.cc.u32 %2, %5, %6, %2;\n\t"
+        "addc.u32 %3, %3, 0;\n\t"
+        "mad.lo.cc.u32 %2, %5, %7, %2;\n\t"
+        "madc.hi.u32 %3, %5, %7, %3;"
+        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3) : "r"(y0), "r"(y1), "r"(c0), "r"(c1));
+    lo = ((u64)a1 << 32) | a0; hi = ((u64)a3 << 32) | a2;
+}
+
+template <bool SC, bool W1, int IC>
 __global__ void __launch_bounds__(BC)
 bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_in_total, int in_start, int in_count,
              int l_out, const u64* __restrict__ q, const tw_t* __restrict__ qhat_inv, const u64* __restrict__ qhat_mod_p,
              const u64* __restrict__ p, const ulonglong2* __restrict__ mu_p, const __grid_constant__ BconvScatter sc) {
-    extern __shared__ u64 sy[];        // [in_count][BC]
+    extern __shared__ u64 sy[];        // [in_count][BC], IC == 0 only
     const size_t d = (size_t)blockIdx.x * BC + threadIdx.x;
     const size_t b = blockIdx.y;
     const bool live = d < N;
     const u64* x = in + b * (size_t)in_count * N;
-    for (int i = 0; i < in_count; ++i) {
-        const int gi = in_start + i;
-        sy[i * BC + threadIdx.x] = live ? mul_shoup(x[(size_t)i * N + d], qhat_inv[gi], q[gi]) : 0;
-    }
-    // each thread reads back only its own column: no barrier needed
-    if (!live) return;
-    u64* o = SC ? nullptr : out + b * (size_t)l_out * N;
-    for (int j = 0; j < l_out; ++j) {
-        u64 lo = 0, hi = 0;
-        const u64* w = qhat_mod_p + (size_t)j * l_in_total + in_start;
+    u64 yr[IC > 0 ? IC : 1];
+    if constexpr (IC > 0) {
+        if (!live) return;
+#pragma unroll
+        for (int i = 0; i < IC; ++i) yr[i] = x[(size_t)i * N + d];
+#pragma unroll
+        for (int i = 0; i < IC; ++i) yr[i] = mul_shoup(yr[i], qhat_inv[in_start + i], q[in_start + i]);
+    } else {
         for (int i = 0; i < in_count; ++i) {
-            const u64 y = sy[i * BC + threadIdx.x], c = __ldg(w + i);
-            const u64 pl = y * c, ph = __umul64hi(y, c);
-            lo += pl; hi += ph + (lo < pl);
+            const int gi = in_start + i;
+            sy[i * BC + threadIdx.x] = live ? mul_shoup(x[(size_t)i * N + d], qhat_inv[gi], q[gi]) : 0;
         }
-        const ulonglong2 m = mu_p[j];
-        u64 r;
-        if constexpr (W1) {
-            const barrett1_t bc = make_barrett1(p[j], m.x, m.y);
-            const u64 x1 = (lo >> bc.sh) | (hi << (64 - bc.sh));
-            r = lo - __umul64hi(x1, bc.mu1) * bc.q;
-            r = csub(csub(r, bc.q2), bc.q);
-        } else {
-            r = reduce128(lo, hi, p[j], m.x, m.y);
-        }
+        // each thread reads back only its own column: no barrier needed
+        if (!live) return;
+    }
+    u64* o = SC ? nullptr : out + b * (size_t)l_out * N;
+    auto put = [&](int j, u64 r) {
         if constexpr (SC) sc.base[j][b * sc.bstride[j] + d] = r;
         else              o[(size_t)j * N + d] = r;
+    };
+    if constexpr (IC > 0) {
+        int j = 0;
+        for (; j + 2 <= l_out; j += 2) {
+            const u64* w0 = qhat_mod_p + (size_t)j * l_in_total + in_start;
+            const u64* w1 = w0 + l_in_total;
+            u64 lo0 = 0, hi0 = 0, lo1 = 0, hi1 = 0;
+#pragma unroll
+            for (int i = 0; i < IC; ++i) {
+                mac128(lo0, hi0, yr[i], __ldg(w0 + i));
+                mac128(lo1, hi1, yr[i], __ldg(w1 + i));
+            }
+            put(j, bconv_fold<W1>(lo0, hi0, p[j], mu_p[j]));
+            put(j + 1, bconv_fold<W1>(lo1, hi1, p[j + 1], mu_p[j + 1]));
+        }
+        if (j < l_out) {
+            const u64* w0 = qhat_mod_p + (size_t)j * l_in_total + in_start;
+            u64 lo0 = 0, hi0 = 0;
+#pragma unroll
+            for (int i = 0; i < IC; ++i) mac128(lo0, hi0, yr[i], __ldg(w0 + i));
+            put(j, bconv_fold<W1>(lo0, hi0, p[j], mu_p[j]));
+        }
+    } else {
+        for (int j = 0; j < l_out; ++j) {
+            u64 lo = 0, hi = 0;
+            const u64* w = qhat_mod_p + (size_t)j * l_in_total + in_start;
+            for (int i = 0; i < in_count; ++i) mac128(lo, hi, sy[i * BC + threadIdx.x], __ldg(w + i));
+            put(j, bconv_fold<W1>(lo, hi, p[j], mu_p[j]));
+        }
     }
 }
 
@@ -155,12 +213,11 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     if (in_start < 0 || in_count < 1 || in_start + in_count > b->l_in) return fail(MFHE_EINVAL, std::string(who) + ": limb window out of range");
     if (!N || !batch) return MFHE_OK;
     if (batch > 65535) return fail(MFHE_EINVAL, std::string(who) + ": batch too large");
-    const size_t smem = (size_t)in_count * BC * 8;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaSuccess;
-        const void* fns[4] = {(const void*)bconv_kernel<false, false>, (const void*)bconv_kernel<false, true>,
-                              (const void*)bconv_kernel<true, false>, (const void*)bconv_kernel<true, true>};
+        const void* fns[4] = {(const void*)bconv_kernel<false, false, 0>, (const void*)bconv_kernel<false, true, 0>,
+                              (const void*)bconv_kernel<true, false, 0>, (const void*)bconv_kernel<true, true, 0>};
         for (const void* f : fns)
             if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, who);
@@ -171,15 +228,31 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     uint64_t qmax = 0;
     for (int i = in_start; i < in_start + in_count; ++i) qmax = std::max(qmax, b->q[i]);
     static const bool force128 = getenv("MFHE_BCONV_128") != nullptr;
+    static const bool generic = getenv("MFHE_BCONV_GENERIC") != nullptr;
     const bool w1 = !force128 && (unsigned __int128)qmax * (unsigned)in_count <= ((unsigned __int128)1 << 61);
     static const BconvScatter none{};
     const BconvScatter& tab = sc ? *sc : none;
-#define MFHE_BCONV_LAUNCH(SCV, W1V)                                                                                        \
-    bconv_kernel<SCV, W1V><<<grid, BC, smem, (cudaStream_t)stream>>>((const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, \
-                                                                    b->l_out, b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p,  \
-                                                                    b->d_mu_p, tab)
-    if (sc) { if (w1) MFHE_BCONV_LAUNCH(true, true); else MFHE_BCONV_LAUNCH(true, false); }
-    else    { if (w1) MFHE_BCONV_LAUNCH(false, true); else MFHE_BCONV_LAUNCH(false, false); }
+#define MFHE_BCONV_LAUNCH(SCV, W1V, ICV)                                                                                   \
+    bconv_kernel<SCV, W1V, ICV><<<grid, BC, (ICV) ? 0 : (size_t)in_count * BC * 8, (cudaStream_t)stream>>>(                  \
+        (const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out, b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p,  \
+        b->d_mu_p, tab)
+#define MFHE_BCONV_IC(ICV)                                                                                 \
+    do {                                                                                                   \
+        if (sc) { if (w1) MFHE_BCONV_LAUNCH(true, true, ICV); else MFHE_BCONV_LAUNCH(true, false, ICV); }   \
+        else    { if (w1) MFHE_BCONV_LAUNCH(false, true, ICV); else MFHE_BCONV_LAUNCH(false, false, ICV); } \
+    } while (0)
+    switch (generic ? 0 : in_count) {          // register-resident forms for the window sizes limb sharding produces
+        case 2: MFHE_BCONV_IC(2); break;
+        case 3: MFHE_BCONV_IC(3); break;
+        case 4: MFHE_BCONV_IC(4); break;
+        case 6: MFHE_BCONV_IC(6); break;
+        case 8: MFHE_BCONV_IC(8); break;
+        case 12: MFHE_BCONV_IC(12); break;
+        case 16: MFHE_BCONV_IC(16); break;
+        case 24: MFHE_BCONV_IC(24); break;
+        default: MFHE_BCONV_IC(0); break;
+    }
+#undef MFHE_BCONV_IC
 #undef MFHE_BCONV_LAUNCH
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
