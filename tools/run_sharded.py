@@ -33,6 +33,8 @@ def main():
                     help="nccl: one all-to-all; pipelined: per batch group, overlapped; p2p: fused partial + peer stores")
     ap.add_argument("--groups", type=int, default=4)
     ap.add_argument("--p2p-groups", type=int, default=1, help="p2p: batch slices alternating between two streams")
+    ap.add_argument("--also-p2p-groups", type=int, default=0,
+                    help="p2p: after the main measurement, time the step again with this many stream groups (second JSON line)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -115,6 +117,20 @@ def main():
                           "parity": ("ok" if ok else "FAILED") if a.check else "not checked"}))
         if a.check:
             print("parity ok" if ok else "parity FAILED")
+    if a.exchange == "p2p" and a.also_p2p_groups > 0:
+        a.p2p_groups = a.also_p2p_groups
+        for _ in range(max(a.warmup, 1)):
+            out = step()
+        torch.cuda.synchronize(); dist.barrier()
+        ev[0].record()
+        for _ in range(a.steps):
+            out = step()
+        ev[1].record(); torch.cuda.synchronize()
+        t = torch.tensor([ev[0].elapsed_time(ev[1]) / a.steps], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(json.dumps({"metric": "limb_sharded_intt_bconv_ntt_polys_per_s", "value": a.batch / (float(t.item()) * 1e-3),
+                              "unit": "polys/s", "n_gpus": world, "ms_per_step": float(t.item()), "p2p_stream_groups": a.p2p_groups}))
     if world > 1:
         dist.destroy_process_group()
     if not ok:
