@@ -146,3 +146,50 @@ def test_scatter_table_addresses_receive_layout(l_out, world, batch, n):
         want = S.emulate_exchange([torch.from_numpy(p) for p in partials], wins, r).numpy()
         got = mem[r][: world * batch * c * n].reshape(world, batch, c, n)
         assert (got == want).all()
+
+
+def _p2p_worker(rank, world, port, bufs, l_out, batch, n, steps, ret):
+    """The step_p2p protocol with host stand-ins: `bufs[phase][r]` are shared-memory tensors playing the ranks'
+    symmetric receive buffers, the stores go through scatter_table's addresses (base 0 = word offsets), dist.barrier()
+    plays the device barrier.  There is NO barrier after the read, as on the device: only the double buffering keeps a
+    fast rank's stores of step k+1 away from a slow rank's reads of step k."""
+    import time
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        wins = S.limb_windows(l_out, world)
+        mine = wins[rank][1]
+        ok = True
+        for step in range(steps):
+            everyone = [torch.from_numpy(np.random.default_rng(1000 * step + r).integers(
+                0, 1 << 60, size=(batch, l_out, n), dtype=np.int64)) for r in range(world)]
+            partial = everyone[rank]
+            want = S.emulate_exchange(everyone, wins, rank)                 # no collective here: nothing else syncs the ranks
+            phase = step & 1
+            ptrs, strides = S.scatter_table([0] * world, wins, rank, batch, n)
+            for j in range(l_out):
+                owner = next(r for r, (s, c) in enumerate(wins) if s <= j < s + c)
+                for b in range(batch):
+                    off = ptrs[j] // 8 + b * strides[j]
+                    bufs[phase][owner][off:off + n] = partial[b, j]
+            dist.barrier()
+            if rank == 0:
+                time.sleep(0.05)                                            # rank 0 reads late, rank 1 runs ahead
+            got = bufs[phase][rank][: world * batch * mine * n].view(world, batch, mine, n).clone()
+            ok = ok and bool(torch.equal(got, want))
+        ret[rank] = ok
+    finally:
+        dist.destroy_process_group()
+
+
+def test_p2p_protocol_world2_shared_memory():
+    world, l_out, batch, n, steps = 2, 5, 2, 16, 6
+    wins = S.limb_windows(l_out, world)
+    cmax = max(c for _, c in wins)
+    bufs = [[torch.full((world * batch * cmax * n,), -1, dtype=torch.int64).share_memory_() for _ in range(world)]
+            for _ in range(2)]
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_p2p_worker, args=(world, _free_port(), bufs, l_out, batch, n, steps, ret), nprocs=world, join=True)
+        assert all(ret[r] for r in range(world))
