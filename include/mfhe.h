@@ -6,8 +6,21 @@
  * mfhe_last_error() returns the message of the last failure on the calling thread.
  * Unless a name ends in _host, data pointers are DEVICE pointers owned by the caller
  * and the work is enqueued asynchronously on `stream` (a cudaStream_t passed as
- * void*; NULL = the legacy default stream, as the reference uses).  Nothing is
- * allocated on the device after plan/context creation.
+ * void*; NULL = the legacy default stream, as the reference uses).  The data path
+ * allocates nothing on the device after plan/context creation; two exceptions, both
+ * outside the timed paths: the *_host entry points allocate (and free) their own
+ * staging buffers, and mfhe_apply_gl_perm uploads its tiny permutation table on first
+ * use of a given n.
+ *
+ * Streams and threads.  A mfhe_ctx owns ONE scratch arena.  Calls on the same context
+ * may come from different streams and different host threads: the enqueue is
+ * serialised by a mutex in the context, and a call on a different stream than the
+ * previous arena user first waits on the device (cudaStreamWaitEvent) for that user
+ * to finish, so live scratch is never shared -- such calls are correct but do not
+ * overlap; use one context per stream for concurrency.  Plans (mfhe_ntt_plan,
+ * mfhe_bconv_plan) hold read-only tables and may be used from any stream / thread.
+ * One process drives one device (the torchrun model): kernel attributes and a few
+ * tiny tables are cached per process for the device that first used them.
  *
  * Each entry point cites the reference interface it replaces ("ph/" =
  * extern/phantom-fhe/).  INTEGRATION.md shows the binding a maintainer of the

@@ -62,6 +62,7 @@ extern "C" void mfhe_ctx_destroy(mfhe_ctx* c) {
     cudaFree(c->d_xyV); cudaFree(c->d_xyVT); cudaFree(c->d_xyVinv); cudaFree(c->d_xyVinvT);
     cudaFree(c->d_crt_Q); cudaFree(c->d_crt_Qhalf); cudaFree(c->d_crt_M); cudaFree(c->d_crt_inv);
     cudaFree(c->arena);
+    if (c->arena_ev) cudaEventDestroy(c->arena_ev);
     if (c->xy_plan) mfhe_ntt_plan_destroy(c->xy_plan);
     delete c;
 }
@@ -210,6 +211,7 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
         const size_t need = 4 * c->T() * 8 + 4 * phi * nn * 16 + (1 << 20);
         c->arena_bytes = std::max(need, p->arena_bytes);
         e = cudaMalloc((void**)&c->arena, c->arena_bytes);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->arena_ev, cudaEventDisableTiming);
     }
     if (e != cudaSuccess) { mfhe_ctx_destroy(c); return cuda_fail(e, "ctx_create"); }
     int rc = mfhe_ntt_plan_create(c->logn, L, c->moduli.data(), MFHE_NTT_PHANTOM_NEGACYCLIC, &c->xy_plan);
@@ -273,7 +275,7 @@ extern "C" int mfhe_wcrt_forward_vector(mfhe_ctx* c, const uint64_t* in, uint64_
 }
 extern "C" int mfhe_wcrt_forward_centered(mfhe_ctx* c, const int64_t* in, int64_t* out, void* s) {
     if (!c || !in || !out) return fail(MFHE_EINVAL, "wcrt_forward_centered: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     u64* tmp = (u64*)c->take(c->T() * 8);                      // [w][limb][n2]
     if (!tmp) return fail(MFHE_ENOMEM, "wcrt_forward_centered: arena too small");
     WcrtArgs a = wcrt_args(c, false);
@@ -285,7 +287,7 @@ extern "C" int mfhe_wcrt_forward_centered(mfhe_ctx* c, const int64_t* in, int64_
 }
 extern "C" int mfhe_wcrt_inverse_centered(mfhe_ctx* c, const int64_t* in, int64_t* out, void* s) {
     if (!c || !in || !out) return fail(MFHE_EINVAL, "wcrt_inverse_centered: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     const size_t total = (size_t)c->phi * c->n2();
     u64* tmp = (u64*)c->take(total * 8);
     if (!tmp) return fail(MFHE_ENOMEM, "wcrt_inverse_centered: arena too small");
@@ -365,7 +367,7 @@ extern "C" int mfhe_big_pair_to_complex(mfhe_ctx* c, const uint64_t* rm, const u
 // ---- encode / decode --------------------------------------------------------------------------------------
 extern "C" int mfhe_encode(mfhe_ctx* c, const double* msg, uint64_t* out_re, uint64_t* out_im, void* s) {
     if (!c || !msg || !out_re || !out_im) return fail(MFHE_EINVAL, "encode: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     const size_t lanes_bytes = (size_t)c->phi * c->n2() * sizeof(double2);
     double2* xy = (double2*)c->take(lanes_bytes);
     double2* wc = (double2*)c->take(lanes_bytes);
@@ -391,7 +393,7 @@ extern "C" int mfhe_encode(mfhe_ctx* c, const double* msg, uint64_t* out_re, uin
 }
 extern "C" int mfhe_encode_lane(mfhe_ctx* c, const double* msg, uint64_t* re, uint64_t* im, void* s) {
     if (!c || !msg || !re || !im) return fail(MFHE_EINVAL, "encode_lane: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     double2* P = (double2*)c->take(c->n2() * sizeof(double2));
     if (!P) return fail(MFHE_ENOMEM, "encode_lane: arena too small");
     cudaError_t e = xy_sandwich_launch(c->d_xyVinv, c->d_xyVinvT, (const double2*)msg, P, c->n, 1, S(s));
@@ -420,14 +422,14 @@ static cudaError_t decode_tail(mfhe_ctx* c, const u64* er, const u64* ei, int la
 }
 extern "C" int mfhe_decode_eval_pair(mfhe_ctx* c, const uint64_t* er, const uint64_t* ei, int layout, double* out, void* s) {
     if (!c || !er || !ei || !out || (layout & ~1)) return fail(MFHE_EINVAL, "decode_eval_pair: bad argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     cudaError_t e = decode_tail(c, (const u64*)er, (const u64*)ei, layout, (double2*)out, S(s));
     if (e == cudaErrorMemoryAllocation) return fail(MFHE_ENOMEM, "decode_eval_pair: arena too small");
     return done(e, "decode_eval_pair");
 }
 extern "C" int mfhe_decode_lane_from_rns_eval(mfhe_ctx* c, const uint64_t* re, const uint64_t* im, double* out, void* s) {
     if (!c || !re || !im || !out) return fail(MFHE_EINVAL, "decode_lane_from_rns_eval: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     double2* P = (double2*)c->take(c->n2() * sizeof(double2));
     if (!P) return fail(MFHE_ENOMEM, "decode_lane_from_rns_eval: arena too small");
     cudaError_t e = crt_to_complex_launch(crt_dev(c), (const u64*)re, (const u64*)im, P, (int)c->n2(), c->L, 1, c->delta, S(s));
@@ -446,7 +448,7 @@ extern "C" int mfhe_sample_ternary(mfhe_ctx* c, uint64_t* out, void* s) { return
 
 extern "C" int mfhe_keygen(mfhe_ctx* c, uint64_t* sk, void* s) {
     if (!c || !sk) return fail(MFHE_EINVAL, "keygen: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     const size_t total = (size_t)c->phi * c->L * c->n;
     u64* sc = (u64*)c->take(total * 8);
     if (!sc) return fail(MFHE_ENOMEM, "keygen: arena too small");
@@ -466,7 +468,7 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
                         const uint64_t* a_coeff, int e_src, const uint64_t* e_re, const uint64_t* e_im, uint64_t* ct_re,
                         uint64_t* ct_im, void* s, const char* who) {
     if (!c || !m_re || !sk || !ct_re || (ct_im && !m_im)) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     const size_t T = c->T();
     cudaStream_t st = S(s);
     const bool two_e = ct_im && e_src == kSrcMem && e_im != e_re;
@@ -524,7 +526,7 @@ extern "C" int mfhe_encrypt_pair_with(mfhe_ctx* c, const uint64_t* m_re, const u
 extern "C" int mfhe_encode_encrypt_pair(mfhe_ctx* c, const double* msg, const uint64_t* sk, uint64_t* ct_re, uint64_t* ct_im,
                                         void* s) {
     if (!c || !msg || !sk || !ct_re || !ct_im) return fail(MFHE_EINVAL, "encode_encrypt_pair: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     const size_t T = c->T(), total = (size_t)c->phi * c->n2(), lanes_bytes = total * sizeof(double2);
     double2* xy = (double2*)c->take(lanes_bytes);
     double2* wc = (double2*)c->take(lanes_bytes);
@@ -574,7 +576,7 @@ extern "C" int mfhe_decrypt_to_eval(mfhe_ctx* c, const uint64_t* ct, const uint6
 extern "C" int mfhe_decrypt_decode(mfhe_ctx* c, const uint64_t* ct_re, const uint64_t* ct_im, const uint64_t* sk,
                                    double* out, void* s) {
     if (!c || !ct_re || !ct_im || !sk || !out) return fail(MFHE_EINVAL, "decrypt_decode: NULL argument");
-    c->arena_reset();
+    ArenaScope arena_scope(c, S(s));
     u64* mr = (u64*)c->take(c->T() * 8);
     u64* mi = (u64*)c->take(c->T() * 8);
     if (!mr || !mi) return fail(MFHE_ENOMEM, "decrypt_decode: arena too small");

@@ -3,6 +3,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <mutex>
 #include <vector>
 #include <cuda_runtime.h>
 
@@ -40,17 +41,39 @@ struct mfhe_ctx {
     mfhe_ntt_plan* xy_plan = nullptr;
     char* arena = nullptr;
     size_t arena_bytes = 0, arena_used = 0;
+    // the arena is one scratch area shared by all calls on this context: calls are serialised on the host by arena_mu
+    // and ordered on the device by arena_ev (recorded when a call has enqueued its last arena user; a later call on a
+    // DIFFERENT stream waits for it before touching the arena) -- see ArenaScope
+    std::mutex arena_mu;
+    cudaEvent_t arena_ev = nullptr;
+    cudaStream_t arena_stream = nullptr;
+    bool arena_busy = false;
 
     size_t n2() const { return (size_t)n * n; }
     size_t T() const { return (size_t)phi * L * n * n; }
-    // bump allocator over the arena reserved at creation (reset at the start of every API call)
-    void arena_reset() { arena_used = 0; }
+    // bump allocator over the arena reserved at creation (reset at the start of every API call by ArenaScope)
     void* take(size_t bytes) {
         size_t off = (arena_used + 255) & ~(size_t)255;
         if (off + bytes > arena_bytes) return nullptr;
         arena_used = off + bytes;
         return arena + off;
     }
+};
+
+// One per API call that takes arena scratch.  Host threads calling into the same context are serialised for the
+// duration of the enqueue; work enqueued on another stream than the previous arena user first waits (on the device,
+// cudaStreamWaitEvent) until that user has finished, so two streams never share live scratch.
+struct ArenaScope {
+    mfhe_ctx* c; cudaStream_t st; std::unique_lock<std::mutex> lk;
+    ArenaScope(mfhe_ctx* c_, cudaStream_t st_) : c(c_), st(st_), lk(c_->arena_mu) {
+        c->arena_used = 0;
+        if (c->arena_busy && c->arena_stream != st && c->arena_ev) cudaStreamWaitEvent(st, c->arena_ev, 0);
+    }
+    ~ArenaScope() {
+        if (c->arena_ev && cudaEventRecord(c->arena_ev, st) == cudaSuccess) { c->arena_stream = st; c->arena_busy = true; }
+    }
+    ArenaScope(const ArenaScope&) = delete;
+    ArenaScope& operator=(const ArenaScope&) = delete;
 };
 
 namespace mfhe {
