@@ -34,10 +34,19 @@ LOGN, LIMBS, BATCH, BITS = 16, 32, 64, 60
 N = 1 << LOGN
 LIMB_POLYS = LIMBS * BATCH
 ALGO_BYTES_PER_TRANSFORM = 16 * N                # 8 B read + 8 B write per coefficient
-# dram__bytes_read.sum + dram__bytes_write.sum of the two launches of one INVERSE transform (rows + columns kernel)
-# of this workload, from the committed `ncu --set full` capture profiles/r1_07_ncu_ntt_summary.txt
-NCU_DRAM_BYTES_INVERSE = int((1.482865 + 1.026216 + 1.073982 + 1.014492) * 1e9)
-NCU_DRAM_BYTES_FORWARD = int((1.074171 + 1.026351 + 1.440122 + 1.026373) * 1e9)
+WORKLOAD = f"N=2^{LOGN} L={LIMBS} batch={BATCH} negacyclic NTT+INTT, {BITS}-bit primes (BASELINE configs[1])"
+CPU_SAMPLE_POLYS = 2                             # both CPU numbers (cpu_baseline and --impl reference) use this sample
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per transform (the two launches of a forward / inverse transform of
+    this workload) from the newest committed `ncu --set full` capture: profiles/ncu_traffic.json names the capture file
+    and the commit it was taken at.  Not live -- DRAM counters need ncu, and a number printed under ncu is never a
+    bench value -- so it is labelled with its source."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        return {"forward_bytes": None, "inverse_bytes": None, "source": "no capture committed"}
 # register-only butterfly rate of the same arithmetic on this GPU (profiles/r1_04_intpipe.log, "CT bfly approx-quotient"):
 # the integer (fmaheavy) pipe, not HBM, binds these kernels -- reported next to the HBM fraction
 INT_PIPE_BFLY_PER_S_PER_SM = 7.02e9
@@ -55,7 +64,7 @@ L24_EXTRA = [17194410241, 17194804993, 17195989249, 17196581377, 17196976129, 17
              17201515777, 17203884289, 17206844929, 17207437057, 17209608193]
 
 
-def secondary_metrics(dev, world, dist, pairs_per_rank=2):
+def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
     """BASELINE configs 3 and 4 on the matrix pipeline (native ring n=64, p=771): device-timed, reported
     next to the headline.  Every rank runs its own (re, im) pairs: batch-sharded, no collective."""
     import torch
@@ -113,6 +122,17 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2):
             out[tag] = {"ms_per_batch": timed(loop, 3), "encode_ms": timed(lambda: g.encode_to_wntt_eval(m), 3),
                         "decrypt_decode_ms": timed(lambda: g.decrypt_and_decode(ct_r, ct_i, zero, dec), 3),
                         "batch": "512 lanes x 64x64 complex fp64 (2^21 values)", "max_err": err}
+            S_bytes = g.T * 8
+            fl = pipeline_floors(g, mods, 4, 6 * S_bytes + 2 * g.phi * g.n2 * 16)     # encode: 32 MiB + 2S, decode: 4S + 32 MiB
+            msb = out[tag]["ms_per_batch"]
+            out[tag]["roofline"] = dict(fl, bound="tensor" if fl["tensor_floor_ms"] > fl["hbm_floor_ms"] else "hbm",
+                                        frac_of_hbm_floor=fl["hbm_floor_ms"] / msb, frac_of_tensor_floor=fl["tensor_floor_ms"] / msb,
+                                        frac=max(fl["hbm_floor_ms"], fl["tensor_floor_ms"]) / msb,
+                                        note="2 forward + 2 inverse W-CRTs per batch dominate: the loop is tensor-bound, not HBM-bound")
+            if with_cpu:
+                cb = cpu_pipeline_sample(L, mods)
+                out[tag]["cpu_baseline"] = {"value": cb["encode_decode_loop_ms"], "unit": "ms/batch", "cores": cb["cores"],
+                                            "kind": cb["kind"], "sample": cb["sample"]}
         else:
             def pipe():
                 for _ in range(pairs_per_rank):
@@ -133,9 +153,177 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2):
                         "pairs_per_rank_per_step": pairs_per_rank, "max_err": max(err, errf),
                         "note": "mfhe_encode_encrypt_pair -> decrypt_and_decode (three_calls: encode -> encrypt_pair -> "
                                 "decrypt_and_decode, identical ciphertexts), one (re, im) pair = 2 ciphertexts of 768 MiB"}
+            S_bytes = g.T * 8
+            fl = pipeline_floors(g, mods, 5, 12 * S_bytes + 4 * g.phi * g.n2 * 16)     # 12 S + 64 MiB, API boundaries materialised
+            msp = ms / pairs_per_rank
+            out[tag]["roofline"] = dict(fl, bound="tensor" if fl["tensor_floor_ms"] > fl["hbm_floor_ms"] else "hbm",
+                                        frac_of_hbm_floor=fl["hbm_floor_ms"] / msp, frac_of_tensor_floor=fl["tensor_floor_ms"] / msp,
+                                        frac=max(fl["hbm_floor_ms"], fl["tensor_floor_ms"]) / msp,
+                                        note="fused form: 3 forward (re, im, a) + 2 inverse W-CRTs per pair")
+            if with_cpu:
+                cb = cpu_pipeline_sample(L, mods)
+                out[tag]["cpu_baseline"] = {"value": cb["pipeline_pair_ms"], "unit": "ms/pair", "cores": cb["cores"],
+                                            "kind": cb["kind"], "sample": cb["sample"],
+                                            "stages_ms": {k: cb[k] for k in ("encode_ms", "encrypt_pair_ms", "decrypt_and_decode_ms")}}
         del g
         torch.cuda.empty_cache()
     return out
+
+
+def gpu_baselines():
+    """The two GPU baselines BASELINE.json's north_star names, timed on THIS box in THIS run: the reference's own CUDA
+    kernels and Phantom's, i.e. the UNMODIFIED sources of /root/reference compiled for sm_100a by baseline/build_ref.py
+    (test infrastructure; the stock flavour = the reference's own CMake flags) and driven by baseline/ref_time.cu.
+    Runs after our own timed region, on rank 0 of a single-GPU run only."""
+    exe = os.path.join(ROOT, "baseline", "_ref", "ref_time_stock")
+    if not os.path.exists(exe):
+        return {"unavailable": "baseline/_ref/ref_time_stock not built (baseline/build_ref.py needs /root/reference)"}
+    out = os.path.join(ROOT, "gpurun_out", "ref_time_bench.json")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    try:
+        r = subprocess.run([exe, out, "2"], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=420)
+        if r.returncode != 0:
+            return {"unavailable": f"ref_time_stock exited {r.returncode}: {r.stderr[-200:]}"}
+        b = json.load(open(out))
+    except Exception as e:                                  # noqa: BLE001 -- a baseline must never take the bench down
+        return {"unavailable": f"ref_time_stock failed: {e!r}"[:300]}
+    ph, rc = b.get("phantom", {}), b.get("reference_cuda", {})
+    b["how"] = ("unmodified /root/reference sources (src/core/*.cu + vendored Phantom), nvcc sm_100a, -O3 --use_fast_math "
+                "-DPHANTOM_USE_CUDA_PTX (CMakeLists.txt:11,14,95-99 with the arch changed), driven by baseline/ref_time.cu; " + b.pop("timing", ""))
+    b["headline_same_workload"] = {
+        "phantom_limb_polys_per_s": ph.get("cfg2_60bit_limb_poly_pairs_per_s"),
+        "what": "nwt_2d_radix8_forward_inplace + backward_inplace, 64 calls per direction on [64][32][65536], 60-bit primes"}
+    b["notes"] = ["Phantom's CKKS encoder returns garbage on sm_100a in this build (ckks_*_max_err): its times are of the "
+                  "code as it runs, not of a verified result",
+                  "reference_cuda.pipeline_max_err is the reference's own decode error on its e2e driver message"]
+    return b
+
+
+def _tensor_peak():
+    try:
+        bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        return bf16 * 1e12, "2 x measured bf16 MAC rate (MEASURED_PEAKS.json; int8 is nominally twice bf16)"
+    except Exception:
+        return 2.25e15, "nominal 4.5 Pop/s int8 dense"
+
+
+def pipeline_floors(g, mods, n_wcrt, algo_bytes):
+    """HBM floor (SURVEY 8(d) algorithmic bytes / measured HBM peak) and tensor floor (#W-CRT x int8 digit MACs / int8
+    peak) of a matrix-pipeline call sequence, in ms."""
+    hbm, _ = peaks()
+    nd = [(int(q).bit_length() + 7) // 8 for q in mods]
+    macs8 = sum(d * d for d in nd) * g.phi * g.phi * g.n2
+    peak8, src = _tensor_peak()
+    return {"hbm_floor_ms": algo_bytes / (hbm * 1e9) * 1e3, "tensor_floor_ms": n_wcrt * macs8 / peak8 * 1e3,
+            "algorithmic_bytes": int(algo_bytes), "wcrt_calls": n_wcrt, "int8_macs_per_wcrt": int(macs8), "tensor_peak_source": src}
+
+
+def cpu_pipeline_sample(L, mods):
+    """CPU baseline of the matrix pipeline: the oracle's encode -> encrypt_pair -> decrypt_and_decode at n = 16, i.e. on
+    1/16 of the n^2 = 4096 independent (y, x) columns of the native ring (same phi = 512 lanes and limbs; the dense W-CRT,
+    ~95 % of the CPU time, is linear in the column count), scaled by 16 and labelled as such."""
+    import oracle as O
+    cores = O.use_all_cores()
+    o = O.SchemeCtx(16, 257, mods, 2.0 ** 35)
+    ell, i = np.meshgrid(np.arange(o.phi, dtype=np.float64), np.arange(o.n2, dtype=np.float64), indexing="ij")
+    msg = ((ell + 0.001 * i) * (1 - 1j)).reshape(-1)
+    sk = o.keygen()
+    t0 = time.perf_counter(); re, im = o.encode(msg); t1 = time.perf_counter()
+    cr, ci = o.encrypt_pair(re, im, sk); t2 = time.perf_counter()
+    out = o.decrypt_and_decode(cr, ci, sk); t3 = time.perf_counter()
+    assert np.abs(out - msg).max() < 1e-3
+    zk = np.zeros_like(sk); zr = np.zeros_like(cr); zi = np.zeros_like(ci); zr[: o.T] = re; zi[: o.T] = im
+    t4 = time.perf_counter(); o.decrypt_and_decode(zr, zi, zk); t5 = time.perf_counter()
+    scale = (64 * 64) / o.n2
+    return {"encode_ms": (t1 - t0) * 1e3 * scale, "encrypt_pair_ms": (t2 - t1) * 1e3 * scale,
+            "decrypt_and_decode_ms": (t3 - t2) * 1e3 * scale, "pipeline_pair_ms": (t3 - t0) * 1e3 * scale,
+            "encode_decode_loop_ms": ((t1 - t0) + (t5 - t4)) * 1e3 * scale,
+            "cores": cores, "kind": "port",
+            "sample": f"oracle pipeline at n=16 (256 of the 4096 (y,x) columns, phi=512, L={L}), one run, times scaled x{scale:.0f}"}
+
+
+def config5_block(dev, world, rank, dist, steps=10):
+    """BASELINE config 5: N = 2^17, 48 -> 16 limbs of 55-bit primes, batch 16: INTT over the input base -> base conversion ->
+    NTT over the output base.  1 GPU: unsharded.  N >= 2: limbs sharded over the ranks, the partial sums leave the
+    base-conversion kernel as peer stores over NVLink (symmetric memory), one device barrier, then reduce + NTT."""
+    import torch
+    import oracle as O
+    from matrix_fhe_gpu_b200 import sharded as SH
+    logn, lin, lout, bits, batch = 17, 48, 16, 55, 16
+    n = 1 << logn
+    primes = [int(v) for v in O.get_primes(n, bits, lin + lout)]
+    q, p = primes[:lin], primes[lin:]
+    sh = SH.LimbShardedBconv(logn, q, p, rank, world)
+    qs, qc = sh.q_windows[rank]; ps, pc = sh.p_windows[rank]
+    idx = (np.arange(batch, dtype=np.uint64)[:, None, None] * np.uint64(lin * n)
+           + np.arange(qs, qs + qc, dtype=np.uint64)[None, :, None] * np.uint64(n)
+           + np.arange(n, dtype=np.uint64)[None, None, :] + np.uint64(42))
+    x_loc = O.splitmix64(idx) % np.asarray(q[qs:qs + qc], dtype=np.uint64).reshape(1, -1, 1)
+    x0 = torch.from_numpy(x_loc.view(np.int64)).to(dev)
+    work = torch.empty_like(x0)
+    kind, groups = "none (one GPU, unsharded)", 1
+    if world > 1:
+        try:
+            sh.enable_p2p(batch)
+            kind, groups = "fused: bconv kernel stores partial sums into the owners' symmetric-memory buffers over NVLink, one device barrier", 2
+        except Exception as e:                              # noqa: BLE001
+            kind = f"NCCL all_to_all of partial sums (symmetric memory unavailable: {e!r})"[:200]
+
+    def step():
+        work.copy_(x0)
+        if world == 1:
+            return sh.step_unsharded(work, batch)
+        if kind.startswith("fused"):
+            return sh.step_p2p(work, batch, groups)
+        return sh.step(work, batch)
+
+    out = None
+    for _ in range(3):
+        out = step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(steps):
+        out = step()
+    ev[1].record(); torch.cuda.synchronize()
+    t = torch.tensor([ev[0].elapsed_time(ev[1]) / steps], device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # parity: poly 0 of this rank's output window against the CPU oracle (INTT + bConv_BEHZ + NTT restated)
+    x_full0 = O.synth_polys(42, 1, q, n)
+    coeff = O.PhantomTables(logn, q).inverse(x_full0)
+    want = O.PhantomTables(logn, p).forward(O.bconv(coeff[0], q, p)[None])[0, ps:ps + pc]
+    ok = bool((out[0].cpu().numpy().view(np.uint64) == want).all())
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    stages = None
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if kind.startswith("fused"):
+            acc = np.zeros(4)
+            for _ in range(5):
+                work.copy_(x0)
+                dist.barrier()
+                _, st = sh.step_p2p_stages(work, batch)
+                acc += np.asarray(st)
+            tt = torch.tensor(acc / 5, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            stages = [float(v) for v in tt.tolist()]
+    sent = batch * (lout - pc) * n * 8 if world > 1 else 0
+    blk = {"polys_per_s": batch / (ms * 1e-3), "ms_per_step": ms, "n_gpus": world,
+           "config": f"N=2^{logn}, {lin} -> {lout} limbs of {bits}-bit primes, batch {batch} (BASELINE configs[4])",
+           "exchange": kind, "stream_groups": groups, "bytes_sent_per_rank": sent,
+           "parity": "ok" if bool(flag.item()) else "FAILED",
+           "parity_check": "poly 0, every rank's output limbs, vs the CPU oracle (INTT + bConv_BEHZ + NTT restated)",
+           "algorithmic_bytes_per_step": batch * n * 8 * (2 * lin + 2 * lout)}
+    if stages:
+        blk["stage_ms"] = {"intt": stages[0], "scatter": stages[1], "barrier": stages[2], "reduce_ntt": stages[3],
+                           "note": "one stream group, CUDA events between the stages, max over ranks"}
+        blk["nvlink_gbs_per_rank"] = sent / (stages[1] * 1e-3) / 1e9 if stages[1] > 0 else None
+        blk["nvlink_note"] = "bytes this rank stores into peers / the scatter kernel's own duration"
+    return blk
 
 
 class ClockSampler:
@@ -221,6 +409,7 @@ class ClockSampler:
 def cpu_sample(sample_limb_polys: int, reps: int):
     """Oracle (CPU restatement of the reference algorithm) on a bounded sample, all host threads."""
     import oracle as O
+    O.use_all_cores()                            # torch.distributed.run exports OMP_NUM_THREADS=1: set and state it
     mods = O.coeff_modulus_create(N, BITS, LIMBS)
     t = O.PhantomTables(LOGN, mods)
     polys = max(1, sample_limb_polys // LIMBS)
@@ -244,18 +433,18 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n_lp, times, cores = cpu_sample(4 * LIMBS, max(1, args.steps))
-    for _ in range(0):
-        pass
-    ms = 1e3 * sum(times) / len(times)
-    value = n_lp / (sum(times) / len(times))
-    sample = f"{n_lp} limb-polys ({n_lp // LIMBS} of {BATCH} polys x {LIMBS} limbs) per step, NTT+INTT, OpenMP"
+    n_lp, times, cores = cpu_sample(CPU_SAMPLE_POLYS * LIMBS, max(1, args.steps))
+    ms = 1e3 * min(times)
+    value = n_lp / min(times)
+    sample = (f"{n_lp} limb-polys ({n_lp // LIMBS} of {BATCH} polys x {LIMBS} limbs) per step, NTT+INTT, OpenMP over "
+              f"{cores} threads, best of {len(times)} steps (same rule as the native arm's cpu_baseline)")
     line = {
         "impl": "reference", "metric": "ntt_intt_limb_polys_per_s", "value": value, "unit": "limb-polys/s",
         "n_gpus": args.gpus, "steps": len(times), "warmup": 1, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": f"N=2^{LOGN} L={LIMBS} batch={BATCH} negacyclic NTT+INTT, {BITS}-bit primes",
-                   "note": "CPU restatement of the reference algorithm (oracle/); the reference ships no CPU path"},
+        "config": {"workload": WORKLOAD,
+                   "note": "CPU restatement of the reference algorithm (oracle/); the reference ships no CPU path: its own "
+                           "CUDA kernels and Phantom's are timed by the native arm as `baselines`"},
         "cpu_baseline": {"value": value, "unit": "limb-polys/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "limb-polys/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -274,6 +463,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the matrix-pipeline secondary metrics")
+    ap.add_argument("--no-baselines", action="store_true", help="skip timing the reference's and Phantom's CUDA kernels")
+    ap.add_argument("--no-config5", action="store_true", help="skip the limb-sharded config-5 block")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -367,7 +558,12 @@ def main():
     if not args.no_secondary:
         del d
         torch.cuda.empty_cache()
-        secondary = secondary_metrics(dev, world, dist if world > 1 else None)
+        secondary = secondary_metrics(dev, world, dist if world > 1 else None, with_cpu=(rank == 0 and world == 1 and not args.no_cpu))
+        if not args.no_config5:
+            try:
+                secondary["config5_limb_sharded"] = config5_block(dev, world, rank, dist if world > 1 else None)
+            except Exception as e:                          # noqa: BLE001 -- report, never lose the headline line
+                secondary["config5_limb_sharded"] = {"error": repr(e)[:400]}
     if rank == 0:
         peak, peak_src = peaks()
         t_fwd = statistics.median(tf) * 1e-3
@@ -379,8 +575,7 @@ def main():
             "metric": "ntt_intt_limb_polys_per_s", "value": value, "unit": "limb-polys/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": f"N=2^{LOGN} L={LIMBS} batch={BATCH} negacyclic NTT+INTT, {BITS}-bit primes "
-                                   f"(BASELINE configs[1])",
+            "config": {"workload": WORKLOAD,
                        "bytes_resident": int(nbytes), "l2": "input (1 GiB) larger than L2, no flush needed",
                        "partition": "batch axis, one batch per GPU, no collective",
                        "chunk_limb_polys": args.chunk},
@@ -392,9 +587,8 @@ def main():
             "gpu_launches": 4 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_INVERSE if t_inv >= t_fwd else NCU_DRAM_BYTES_FORWARD,
-                         "traffic_note": "two launches (row + column kernel) = two passes over the data; ncu capture "
-                                         "profiles/r1_07_ncu_ntt_summary.txt",
+                         "traffic": ncu_traffic()["inverse_bytes" if t_inv >= t_fwd else "forward_bytes"],
+                         "traffic_note": "dram read+write bytes of the two launches of that transform; " + str(ncu_traffic().get("source")),
                          "algorithmic_bytes_per_launch_pair": algo,
                          "int_pipe": {"butterflies_per_s": LIMB_POLYS * (N // 2) * LOGN / worst,
                                       "peak_butterflies_per_s": INT_PIPE_BFLY_PER_S_PER_SM * 148,
@@ -411,10 +605,13 @@ def main():
         if secondary is not None:
             line["secondary"] = secondary
         if not args.no_cpu:
-            n_lp, times, cores = cpu_sample(2 * LIMBS, 3)
+            n_lp, times, cores = cpu_sample(CPU_SAMPLE_POLYS * LIMBS, 3)
             line["cpu_baseline"] = {"value": n_lp / min(times), "unit": "limb-polys/s", "cores": cores,
                                     "kind": "port",
-                                    "sample": f"{n_lp} limb-polys (2 of {BATCH} polys x {LIMBS} limbs), NTT+INTT, best of 3"}
+                                    "sample": f"{n_lp} limb-polys ({CPU_SAMPLE_POLYS} of {BATCH} polys x {LIMBS} limbs), NTT+INTT, "
+                                              f"OpenMP over {cores} threads, best of 3"}
+        if world == 1 and not args.no_baselines:
+            line["baselines"] = gpu_baselines()
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -132,6 +132,17 @@ class LimbShardedBconv:
         self.plan_p.forward_limbs_(out, ps, pc)
         return out.view(batch, pc, self.n)
 
+    def step_unsharded(self, x, batch: int):
+        """world == 1: the whole config-5 step on one GPU with no partial / reduce split: INTT over all Q limbs ->
+        mfhe_bconv -> NTT over all P limbs (what Phantom does with nwt_2d_radix8_backward_inplace + bConv_BEHZ +
+        nwt_2d_radix8_forward_inplace, one call per poly)."""
+        if self.world != 1:
+            raise RuntimeError("step_unsharded: single-rank form")
+        self.plan_q.inverse_(x)
+        out = self.bconv.convert(x, self.n, batch)
+        self.plan_p.forward_(out)
+        return out.view(batch, len(self.p), self.n)
+
     def step(self, x_local, batch: int):
         partial = self.local_partial(x_local, batch)
         parts = exchange_partials(partial, self.p_windows, self.rank, self.world, self.group)
@@ -232,3 +243,28 @@ class LimbShardedBconv:
         hdl.barrier(channel=0)          # stream-ordered: every rank's stores are complete and visible after it
         parts = buf[: self.world * batch * mine * self.n].view(self.world, batch, mine, self.n)
         return self.finish(parts, batch)
+
+    def step_p2p_stages(self, x_local, batch: int):
+        """step_p2p (one stream group) with a CUDA event between the stages; returns (out, [ms_intt, ms_scatter,
+        ms_barrier, ms_reduce_ntt]).  bench.py divides the bytes a rank sends by ms_scatter -- the scatter kernel's own
+        duration -- for the achieved NVLink egress."""
+        import torch
+        if getattr(self, "_p2p", None) is None or self._p2p_batch != batch:
+            raise RuntimeError("step_p2p_stages: call enable_p2p(batch) first")
+        buf, hdl, ptrs, strides = self._p2p[self._p2p_phase]
+        self._p2p_phase ^= 1
+        qs, qc = self.q_windows[self.rank]
+        mine = self.p_windows[self.rank][1]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        ev[0].record()
+        self.plan_q.inverse_limbs_(x_local, qs, qc)
+        ev[1].record()
+        self.bconv.partial_scatter(x_local, qs, qc, ptrs, strides, self.n, batch)
+        ev[2].record()
+        hdl.barrier(channel=0)
+        ev[3].record()
+        parts = buf[: self.world * batch * mine * self.n].view(self.world, batch, mine, self.n)
+        out = self.finish(parts, batch)
+        ev[4].record()
+        torch.cuda.synchronize()
+        return out, [ev[i].elapsed_time(ev[i + 1]) for i in range(4)]

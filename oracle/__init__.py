@@ -73,6 +73,7 @@ def lib() -> C.CDLL:
         L.mfo_negacyclic_inverse_batch.argtypes = [_p64, C.c_size_t, C.c_size_t, C.c_int,
                                                    _p64, _p64, _p64, _p64, _p64]
         L.mfo_num_threads.restype = C.c_int
+        L.mfo_set_num_threads.restype = None; L.mfo_set_num_threads.argtypes = [C.c_int]
         L.mfo_gl_get_psi.restype = u64; L.mfo_gl_get_psi.argtypes = [u64, C.c_int]
         for name in ("mfo_gl_forward", "mfo_gl_backward", "mfo_cyclic_forward", "mfo_cyclic_backward"):
             getattr(L, name).restype = None
@@ -103,6 +104,17 @@ def ref():
 
 
 # ---------------------------------------------------------------- helpers ----
+def use_all_cores() -> int:
+    """Sets the oracle's OpenMP thread count to the cores this process may run on (torch.distributed.run exports
+    OMP_NUM_THREADS=1, which would otherwise make the CPU arm single-threaded); returns the count."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    lib().mfo_set_num_threads(n)
+    return lib().mfo_num_threads()
+
+
 def get_primes(ntt_size: int, bits: int, count: int) -> np.ndarray:
     out = np.zeros(count, dtype=np.uint64)
     if lib().mfo_get_primes(ntt_size, bits, count, out) != 0:

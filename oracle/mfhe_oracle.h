@@ -79,6 +79,7 @@ void mfo_negacyclic_inverse_batch(uint64_t *data, size_t batch, size_t L, int lo
                                   const uint64_t *itw, const uint64_t *itw_shoup,
                                   const uint64_t *n_inv, const uint64_t *n_inv_shoup);
 int mfo_num_threads(void);
+void mfo_set_num_threads(int n);
 
 /* ---- reference "gl" convention, ring Z_q[X]/(X^n - i) ------------------- */
 /* src/core/ntt_core.cu:49-70 get_psi: smallest base >= 2 giving order 4n.   */

@@ -233,6 +233,15 @@ int mfo_num_threads(void) {
 #endif
 }
 
+/* bench.py: torch.distributed.run exports OMP_NUM_THREADS=1; the CPU arm states and sets its thread count itself */
+void mfo_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ---- reference gl convention ------------------------------------------------ */
 /* src/core/ntt_core.cu:49-70 */
 uint64_t mfo_gl_get_psi(uint64_t q, int n) {

@@ -82,14 +82,17 @@ def test_partial_scatter_matches_partial_plus_exchange(cuda_device, logn, l_in, 
         assert bool((bufs[r][world * batch * c * N:] == -1).all())         # nothing written past the window
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p"])
+@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p", "p2p-groups2"])
 def test_limb_sharded_step_nccl(exchange):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", "29631", os.path.join(ROOT, "tools", "run_sharded.py"), "--logn", "13", "--lin", "6", "--lout", "4",
-           "--batch", "3" if exchange == "pipelined" else "2", "--check", "--steps", "3", "--exchange", exchange]
+           "--batch", "3" if exchange in ("pipelined", "p2p-groups2") else "2", "--check", "--steps", "3",
+           "--exchange", exchange.split("-")[0]]
+    if exchange == "p2p-groups2":        # the two-stream form behind the config-5 number; a batch that does not divide evenly
+        cmd += ["--p2p-groups", "2"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "parity ok" in r.stdout

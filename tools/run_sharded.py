@@ -95,6 +95,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     ok = True
+    want = None
     if a.check:
         coeff = O.PhantomTables(a.logn, q).inverse(x_full)
         conv = np.stack([O.bconv(coeff[b], q, p) for b in range(a.batch)])
@@ -128,9 +129,17 @@ def main():
         ev[1].record(); torch.cuda.synchronize()
         t = torch.tensor([ev[0].elapsed_time(ev[1]) / a.steps], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ok2 = True
+        if a.check:                                      # the second form is parity-checked like the first
+            ok2 = bool((out.cpu().numpy().view(np.uint64) == want).all())
+            flag = torch.tensor([1 if ok2 else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            ok2 = bool(flag.item())
+            ok = ok and ok2
         if rank == 0:
             print(json.dumps({"metric": "limb_sharded_intt_bconv_ntt_polys_per_s", "value": a.batch / (float(t.item()) * 1e-3),
-                              "unit": "polys/s", "n_gpus": world, "ms_per_step": float(t.item()), "p2p_stream_groups": a.p2p_groups}))
+                              "unit": "polys/s", "n_gpus": world, "ms_per_step": float(t.item()), "p2p_stream_groups": a.p2p_groups,
+                              "parity": ("ok" if ok2 else "FAILED") if a.check else "not checked"}))
     if world > 1:
         dist.destroy_process_group()
     if not ok:
