@@ -112,6 +112,22 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
                                                     "frac": macs8 / (ms_w * 1e-3) / peak8, "peak_source": src},
                                        "kernel": "wcrt_umma_kernel (tcgen05.mma kind::i8), profiles/r1_12_ncu_umma_summary.txt"}
             del a_u
+            # encrypted matrix product: four Gaussian-integer GEMMs on the ciphertext components
+            # (mma.sync u8 digit GEMMs, K = 2n) + the 4-term decryption
+            prod = g.ct_matmul(cr, ci, cr, ci)
+            ms_mm = timed(lambda: g.ct_matmul(cr, ci, cr, ci), 3)
+            ms_md = timed(lambda: g.ct_matmul_decrypt(prod, sk), 3)
+            macs_mm = 4 * 4 * sum(d * d for d in nd) * g.phi * g.n ** 3      # 4 GEMMs x 4 real products x digit pairs
+            out["encrypted_matmul_L11"] = {
+                "ct_matmul_ms": ms_mm, "ct_matmul_decrypt_ms": ms_md,
+                "lane_products_per_s": g.phi / ((ms_mm + ms_md) * 1e-3),
+                "what": "512 lanes of 64x64 complex matrices: R_l = V_l^H U_l from two (re, im) ciphertext pairs",
+                "roofline": {"bound": "hbm", "algorithmic_bytes": int(16 * g.T * 8),
+                             "achieved": 16 * g.T * 8 / (ms_mm * 1e-3) / 1e9, "peak": peaks()[0], "unit": "GB/s",
+                             "frac": 16 * g.T * 8 / (ms_mm * 1e-3) / 1e9 / peaks()[0],
+                             "int8_macs_per_s": macs_mm / (ms_mm * 1e-3),
+                             "note": "ct_matmul: 4 x (read 4 S + write 2 S); legacy mma.sync path, the tcgen05 form is the W-CRT's"}}
+            del prod
             zero = torch.zeros_like(sk)
             ct_r, ct_i = g.allocate_ciphertext(), g.allocate_ciphertext()
 

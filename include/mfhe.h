@@ -263,6 +263,25 @@ int mfhe_trace_rescale(mfhe_ctx *ctx, uint64_t *d_Cr, uint64_t *d_Ci, int batch,
                        uint64_t inv2, void *stream);
 
 /* ---- GL permutation (src/core/ntt_core.cu:150-173, 433-441) --------------------------------------- */
+/* ---- encrypted matrix product: SURVEY 8(f) rank 1.  The reference ships the pieces (multiply_ciphertexts_raw
+ * HE.cu:1727-1740, the trace step trace.cu:30-161 / batched_trace.cu:37-197) but no caller; these entry points wire the
+ * trace GEMM onto ciphertexts.  Layout of every operand: poly sets [w][l][y][x] (MFHE_LAYOUT_MATRIX). ---- */
+/* trace.cu:30-62 with the twist along x (the fast index of this layout) instead of the slow one: applied to an ENCODED
+ * plaintext before encryption; batch = number of (lane) matrices per limb set, i.e. phi for a full poly set */
+int mfhe_trace_map_x(mfhe_ctx *ctx, const uint64_t *d_Br, const uint64_t *d_Bi, uint64_t *d_Bpr, uint64_t *d_Bpi, int batch, void *stream);
+/* trace.cu:77-120 contracting over the SLOW index: D[x][z] = n * sum_y U[y][x] V[y][z] (complex, mod q), tensor cores */
+int mfhe_trace_gemm_ty(mfhe_ctx *ctx, const uint64_t *d_Ur, const uint64_t *d_Ui, const uint64_t *d_Vr, const uint64_t *d_Vi,
+                       uint64_t *d_Dr, uint64_t *d_Di, int batch, void *stream);
+/* every n x n matrix of a [count][n][n] array transposed */
+int mfhe_transpose(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, size_t count, void *stream);
+/* trace.cu:132-161 repaired: limb l is multiplied by h_inv[l] (HOST array of L constants) */
+int mfhe_trace_rescale_limbs(mfhe_ctx *ctx, uint64_t *d_Cr, uint64_t *d_Ci, int batch, const uint64_t *h_inv, void *stream);
+/* the four component GEMMs of two ciphertext pairs; d_out = 8 poly sets [bb re, im | ab re, im | ba re, im | aa re, im] */
+int mfhe_ct_matmul(mfhe_ctx *ctx, const uint64_t *d_ctU_re, const uint64_t *d_ctU_im, const uint64_t *d_ctV_re,
+                   const uint64_t *d_ctV_im, uint64_t *d_out, void *stream);
+/* decrypts the 4-component product (d_prod is consumed as scratch); out = evals [w][l][z][x] of n * sum_y U V' */
+int mfhe_ct_matmul_decrypt(mfhe_ctx *ctx, uint64_t *d_prod, const uint64_t *d_sk, uint64_t *d_out_re, uint64_t *d_out_im, void *stream);
+
 int mfhe_gl_perm_tables(int n, uint32_t *h_perm, uint32_t *h_inv_perm);
 int mfhe_apply_gl_perm(const uint64_t *d_in, uint64_t *d_out, int limbs, int batch_count, int n, int inverse, void *stream);
 

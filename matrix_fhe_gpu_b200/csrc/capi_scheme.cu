@@ -626,6 +626,76 @@ extern "C" int mfhe_trace_rescale(mfhe_ctx* c, uint64_t* Cr, uint64_t* Ci, int b
                 "trace_rescale");
 }
 
+// ---- encrypted matrix product -------------------------------------------------------------
+// The slot matrix of a lane is M[a][b] = m(X = xi_b, Y = xi_a) with xi^n = i; the secret key depends on X only, so a
+// contraction over the Y index of two ciphertexts is a plain GEMM on their component matrices -- no ring product, no
+// relinearisation inside the sum.  With U = (b_U | a_U) and V' = (b_V' | a_V'), V' the X-twisted encoding of V
+// (mfhe_trace_map_x, the map of trace.cu:30-62 along x):
+//     D_uv[x][z] = n * sum_y  u[y][x] * v'[y][z]      u in {b_U, a_U}, v' in {b_V', a_V'}     (Gaussian integers mod q)
+// and  D_bb + D_ab (*)_x s + D_ba (*)_z s + D_aa (*)_x s (*)_z s  decrypts to  n * sum_y U[y][x] V'[y][z]  (+ noise),
+// the coefficient matrix in (X, Z) of  R[b][b'] = sum_a M_U[a][b] conj(M_V[a][b'])  (derivation in DESIGN.md).
+extern "C" int mfhe_trace_map_x(mfhe_ctx* c, const uint64_t* Br, const uint64_t* Bi, uint64_t* Bpr, uint64_t* Bpi, int batch, void* s) {
+    if (!c || !Br || !Bi || !Bpr || !Bpi || batch < 1 || Br == Bpr || Bi == Bpi) return fail(MFHE_EINVAL, "trace_map_x: bad argument");
+    return done(trace_map_launch((const u64*)Br, (const u64*)Bi, (u64*)Bpr, (u64*)Bpi, c->d_moduli, c->n, c->L, batch, S(s), 1), "trace_map_x");
+}
+static cudaError_t gemm_ty(mfhe_ctx* c, const u64* Ur, const u64* Ui, const u64* Vr, const u64* Vi, u64* Dr, u64* Di, int batch,
+                           cudaStream_t st) {
+    static const bool pin_cuda_core = [] { const char* e = std::getenv("MFHE_TRACE_PATH"); return e && e[0] == 'c'; }();
+    if (!pin_cuda_core && trace_gemm_tc_eligible(c->n, c->L, c->ndig.data()))
+        return trace_gemm_tc_launch(Ur, Ui, Vr, Vi, Dr, Di, c->d_moduli, c->d_mu, c->ndig.data(), c->L, batch, st, 1);
+    return trace_gemm_launch(Ur, Ui, Vr, Vi, Dr, Di, c->d_moduli, c->d_mu, c->n, c->L, batch, st, 1);
+}
+extern "C" int mfhe_trace_gemm_ty(mfhe_ctx* c, const uint64_t* Ur, const uint64_t* Ui, const uint64_t* Vr, const uint64_t* Vi,
+                                  uint64_t* Dr, uint64_t* Di, int batch, void* s) {
+    if (!c || !Ur || !Ui || !Vr || !Vi || !Dr || !Di || batch < 1) return fail(MFHE_EINVAL, "trace_gemm_ty: bad argument");
+    return done(gemm_ty(c, (const u64*)Ur, (const u64*)Ui, (const u64*)Vr, (const u64*)Vi, (u64*)Dr, (u64*)Di, batch, S(s)), "trace_gemm_ty");
+}
+extern "C" int mfhe_transpose(mfhe_ctx* c, const uint64_t* in, uint64_t* out, size_t count, void* s) {
+    if (!c || !in || !out || in == out) return fail(MFHE_EINVAL, "transpose: bad argument");
+    return done(transpose_launch((const u64*)in, (u64*)out, c->n, count, S(s)), "transpose");
+}
+extern "C" int mfhe_trace_rescale_limbs(mfhe_ctx* c, uint64_t* Cr, uint64_t* Ci, int batch, const uint64_t* h_inv, void* s) {
+    if (!c || !Cr || !Ci || !h_inv || batch < 1) return fail(MFHE_EINVAL, "trace_rescale_limbs: bad argument");
+    RescaleConsts k{};
+    for (int l = 0; l < c->L; ++l) k.inv[l] = h_inv[l];
+    return done(trace_rescale_limbs_launch((u64*)Cr, (u64*)Ci, c->d_moduli, c->d_mu, c->n, c->L, batch, k, S(s)), "trace_rescale_limbs");
+}
+// out: 8 poly sets [D_bb re, im | D_ab re, im | D_ba re, im | D_aa re, im], each [w][l][x][z]
+extern "C" int mfhe_ct_matmul(mfhe_ctx* c, const uint64_t* ctU_re, const uint64_t* ctU_im, const uint64_t* ctV_re,
+                              const uint64_t* ctV_im, uint64_t* out, void* s) {
+    if (!c || !ctU_re || !ctU_im || !ctV_re || !ctV_im || !out) return fail(MFHE_EINVAL, "ct_matmul: NULL argument");
+    const size_t T = c->T();
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < 4 && e == cudaSuccess; ++k) {
+        const size_t uo = (k & 1) ? T : 0, vo = (k & 2) ? T : 0;      // k: 0 bb, 1 ab, 2 ba, 3 aa
+        e = gemm_ty(c, (const u64*)ctU_re + uo, (const u64*)ctU_im + uo, (const u64*)ctV_re + vo, (const u64*)ctV_im + vo,
+                    (u64*)out + (size_t)(2 * k) * T, (u64*)out + (size_t)(2 * k + 1) * T, c->phi, S(s));
+    }
+    return done(e, "ct_matmul");
+}
+// prod (the 8 poly sets of mfhe_ct_matmul) is CONSUMED (used as scratch); out_re / out_im: [w][l][z][x] evals of the product
+extern "C" int mfhe_ct_matmul_decrypt(mfhe_ctx* c, uint64_t* prod, const uint64_t* sk, uint64_t* out_re, uint64_t* out_im, void* s) {
+    if (!c || !prod || !sk || !out_re || !out_im) return fail(MFHE_EINVAL, "ct_matmul_decrypt: NULL argument");
+    const size_t T = c->T();
+    u64* D = (u64*)prod;
+    cudaStream_t st = S(s);
+    auto rows = [&](const u64* mr, const u64* mi, const u64* ar, const u64* ai, u64* o_r, u64* o_i) {
+        RowArgs r;                                      // (o_r, o_i) = (mr, mi) + (ar, ai) (*) s along the fast index
+        r.a = ar; r.a1 = ai; r.s = (const u64*)sk; r.m0 = mr; r.o0 = o_r; r.m1 = mi; r.o1 = o_i;
+        r.subtract = 0; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
+        return xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+    };
+    const size_t mats = (size_t)c->phi * c->L;
+    // 1. D_bb += D_ba (*)_z s      2. D_ab += D_aa (*)_z s      (in place)
+    cudaError_t e = rows(D, D + T, D + 4 * T, D + 5 * T, D, D + T);
+    if (e == cudaSuccess) e = rows(D + 2 * T, D + 3 * T, D + 6 * T, D + 7 * T, D + 2 * T, D + 3 * T);
+    // 3. transposes into the two free pairs: [x][z] -> [z][x]
+    for (int k = 0; k < 4 && e == cudaSuccess; ++k) e = transpose_launch(D + (size_t)k * T, D + (size_t)(4 + k) * T, c->n, mats, st);
+    // 4. out = (D_bb)^T + (D_ab)^T (*)_x s
+    if (e == cudaSuccess) e = rows(D + 4 * T, D + 5 * T, D + 6 * T, D + 7 * T, (u64*)out_re, (u64*)out_im);
+    return done(e, "ct_matmul_decrypt");
+}
+
 // ---- GL permutation -----------------------------------------------------------------------------------------
 // ntt_core.cu:150-173: perm[j] = bitrev((5^j mod 4n - 1) / 4)
 extern "C" int mfhe_gl_perm_tables(int n, uint32_t* perm, uint32_t* inv_perm) {

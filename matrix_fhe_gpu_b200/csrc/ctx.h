@@ -162,13 +162,18 @@ cudaError_t ct_add_launch(const u64* c1, const u64* c2, u64* res, const u64* mod
 cudaError_t ct_mul_launch(const u64* c1, const u64* c2, u64* d0, u64* d1, u64* d2, const u64* moduli, const ulonglong2* mu,
                           size_t T, int n, int limbs, int ref_index, cudaStream_t st);
 cudaError_t trace_map_launch(const u64* Br, const u64* Bi, u64* Bpr, u64* Bpi, const u64* moduli, int n, int limbs,
-                             int batch, cudaStream_t st);
+                             int batch, cudaStream_t st, int axis = 0);
+cudaError_t transpose_launch(const u64* in, u64* out, int n, size_t count, cudaStream_t st);
+struct RescaleConsts { u64 inv[64]; };
+cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
+                                       const RescaleConsts& k, cudaStream_t st);
 bool trace_gemm_tc_eligible(int n, int limbs, const int* h_ndig);
 cudaError_t trace_gemm_tc_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
                                  const u64* moduli, const ulonglong2* mu, const int* h_ndig, int limbs, int batch,
-                                 cudaStream_t st);
+                                 cudaStream_t st, int transposed = 0);
 cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
-                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st);
+                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st,
+                              int transposed = 0);
 cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                  u64 inv0, u64 inv1, u64 inv2, cudaStream_t st);
 cudaError_t gl_perm_launch(const u64* in, u64* out, const uint32_t* perm, int limbs, int batch, int n, cudaStream_t st);

@@ -214,22 +214,41 @@ cudaError_t ct_mul_launch(const u64* c1, const u64* c2, u64* d0, u64* d1, u64* d
 
 // ---- trace step -----------------------------------------------------------------------------------------
 // trace.cu:30-62 / batched_trace.cu:37-79:  B'[(-j mod n)][k] = (a, -b) for j = 0, (-b, -a) otherwise
+// axis 0: the twisted index is the slow one (the reference's [X power][Y power] convention); axis 1: the fast one (x of the
+// ciphertext layout [y][x]) -- the form the encrypted matrix product needs (mfhe_trace_map_x)
 __global__ void trace_map_kernel(const u64* __restrict__ Br, const u64* __restrict__ Bi, u64* __restrict__ Bpr,
-                                 u64* __restrict__ Bpi, const u64* __restrict__ moduli, int n, int limbs, size_t total) {
+                                 u64* __restrict__ Bpi, const u64* __restrict__ moduli, int n, int limbs, size_t total, int axis) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
     const size_t n2 = (size_t)n * n, mat = idx / n2, pos = idx % n2;
     const int j = (int)(pos / n), k = (int)(pos % n), l = (int)(mat % limbs);
     const u64 q = moduli[l];
-    const size_t dst = mat * n2 + (size_t)((n - j) & (n - 1)) * n + k;
+    const int t = axis ? k : j;
+    const size_t dst = mat * n2 + (axis ? (size_t)j * n + ((n - k) & (n - 1)) : (size_t)((n - j) & (n - 1)) * n + k);
     const u64 a = Br[idx], b = Bi[idx];
-    if (j == 0) { Bpr[dst] = a; Bpi[dst] = neg_mod(b, q); }
+    if (t == 0) { Bpr[dst] = a; Bpi[dst] = neg_mod(b, q); }
     else { Bpr[dst] = neg_mod(b, q); Bpi[dst] = neg_mod(a, q); }
 }
 cudaError_t trace_map_launch(const u64* Br, const u64* Bi, u64* Bpr, u64* Bpi, const u64* moduli, int n, int limbs,
-                             int batch, cudaStream_t st) {
+                             int batch, cudaStream_t st, int axis) {
     const size_t total = (size_t)batch * limbs * n * n;
-    trace_map_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(Br, Bi, Bpr, Bpi, moduli, n, limbs, total);
+    trace_map_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(Br, Bi, Bpr, Bpi, moduli, n, limbs, total, axis);
+    return cudaGetLastError();
+}
+
+// every n x n matrix of a [count][n][n] array transposed (shared-memory tile, both sides coalesced)
+__global__ void __launch_bounds__(256)
+transpose_kernel(const u64* __restrict__ in, u64* __restrict__ out, int n) {
+    extern __shared__ u64 sm_tp[];
+    const int ld = n + 1;
+    const size_t base = (size_t)blockIdx.x * n * n;
+    for (int i = threadIdx.x; i < n * n; i += blockDim.x) sm_tp[(i / n) * ld + (i % n)] = in[base + i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < n * n; i += blockDim.x) out[base + i] = sm_tp[(i % n) * ld + (i / n)];
+}
+cudaError_t transpose_launch(const u64* in, u64* out, int n, size_t count, cudaStream_t st) {
+    if (!count) return cudaSuccess;
+    transpose_kernel<<<(unsigned)count, 256, (size_t)n * (n + 1) * sizeof(u64), st>>>(in, out, n);
     return cudaGetLastError();
 }
 
@@ -245,7 +264,7 @@ __device__ __forceinline__ void mac128(acc128& s, u64 a, u64 b) {
 __global__ void __launch_bounds__(256)
 trace_gemm_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, const u64* __restrict__ Bpr,
                   const u64* __restrict__ Bpi, u64* __restrict__ Cr, u64* __restrict__ Ci,
-                  const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu_tab, int n, int limbs) {
+                  const u64* __restrict__ moduli, const ulonglong2* __restrict__ mu_tab, int n, int limbs, int tr) {
     extern __shared__ u64 sm_tr[];
     const int ld = n + 1;
     u64 *sAr = sm_tr, *sAi = sAr + (size_t)n * ld, *sBr = sAi + (size_t)n * ld, *sBi = sBr + (size_t)n * ld;
@@ -253,7 +272,7 @@ trace_gemm_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, const 
     const int l = blockIdx.x % limbs;
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
     for (size_t i = threadIdx.x; i < n2; i += blockDim.x) {
-        const int row = (int)(i / n), t = (int)(i % n);
+        const int row = tr ? (int)(i % n) : (int)(i / n), t = tr ? (int)(i / n) : (int)(i % n);   // tr: operands are K-major
         sAr[t * ld + row] = Ar[base + i]; sAi[t * ld + row] = Ai[base + i];
         sBr[t * ld + row] = Bpr[base + i]; sBi[t * ld + row] = Bpi[base + i];
     }
@@ -273,7 +292,8 @@ trace_gemm_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, const 
     }
 }
 cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
-                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st) {
+                              const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch, cudaStream_t st,
+                              int transposed) {
     const size_t smem = 4 * (size_t)n * (n + 1) * sizeof(u64);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     static bool attr_set = false;
@@ -282,7 +302,7 @@ cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, cons
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    trace_gemm_kernel<<<(unsigned)(batch * limbs), 256, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, n, limbs);
+    trace_gemm_kernel<<<(unsigned)(batch * limbs), 256, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, n, limbs, transposed);
     return cudaGetLastError();
 }
 
@@ -304,6 +324,25 @@ __global__ void trace_rescale_kernel(u64* __restrict__ Cr, u64* __restrict__ Ci,
         Ci[idx] = mul_barrett(Ci[idx], inv, q, mu.x, mu.y);
     }
 }
+// every limb multiplied by its own constant (the repaired form of the rescale step: the reference's kernel only knows
+// three constants, a leftover of a 3-limb design -- SURVEY H7)
+__global__ void trace_rescale_limbs_kernel(u64* __restrict__ Cr, u64* __restrict__ Ci, const u64* __restrict__ moduli,
+                                           const ulonglong2* __restrict__ mu_tab, int n, int limbs, size_t total,
+                                           const __grid_constant__ RescaleConsts k) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int l = (int)((idx / ((size_t)n * n)) % limbs);
+    const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
+    Cr[idx] = mul_barrett(Cr[idx], k.inv[l], q, mu.x, mu.y);
+    Ci[idx] = mul_barrett(Ci[idx], k.inv[l], q, mu.x, mu.y);
+}
+cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
+                                       const RescaleConsts& k, cudaStream_t st) {
+    const size_t total = (size_t)batch * limbs * n * n;
+    trace_rescale_limbs_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(Cr, Ci, moduli, mu, n, limbs, total, k);
+    return cudaGetLastError();
+}
+
 cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                  u64 inv0, u64 inv1, u64 inv2, cudaStream_t st) {
     const size_t total = (size_t)batch * limbs * n * n;

@@ -29,8 +29,28 @@ __device__ __forceinline__ void mma_u8_t(int (&c)[4], const u32 (&a)[4], u32 b0,
 }
 
 // 64 x 64 residues (row-major, K contiguous) -> digit planes [ND][64][TRS] at K byte offset koff; NEG: q - x
-template <int ND, bool NEG>
+// TR: the source is K-major (src[k][row], the encrypted matrix product contracts over the SLOW index of the
+// ciphertext matrices): a thread still reads four consecutive words of the source, which are now four rows of one k,
+// and scatters their digits with byte stores
+template <int ND, bool NEG, bool TR>
 __device__ __forceinline__ void stage_digits(unsigned char* dst, const u64* __restrict__ src, int koff, u64 q) {
+    if constexpr (TR) {
+#pragma unroll
+        for (int r = 0; r < TN * TN / 4 / TTH; ++r) {
+            const int id = threadIdx.x + TTH * r, k = id >> 4, quad = id & 15;
+            const ulonglong2 v01 = *reinterpret_cast<const ulonglong2*>(src + k * TN + quad * 4);
+            const ulonglong2 v23 = *reinterpret_cast<const ulonglong2*>(src + k * TN + quad * 4 + 2);
+            u64 x[4] = {v01.x, v01.y, v23.x, v23.y};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (NEG) x[j] = q - x[j];
+                unsigned char* d = dst + (quad * 4 + j) * TRS + koff + k;
+#pragma unroll
+                for (int v = 0; v < ND; ++v) d[v * TN * TRS] = (unsigned char)(x[j] >> (8 * v));
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int r = 0; r < TN * TN / 4 / TTH; ++r) {
         const int id = threadIdx.x + TTH * r, row = id >> 4, quad = id & 15;
@@ -53,7 +73,7 @@ __device__ __forceinline__ void stage_digits(unsigned char* dst, const u64* __re
     }
 }
 
-template <int ND>
+template <int ND, bool TR>
 __global__ void __launch_bounds__(TTH, 2)
 trace_gemm_tc_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, const u64* __restrict__ Bpr,
                      const u64* __restrict__ Bpi, u64* __restrict__ Cr, u64* __restrict__ Ci,
@@ -68,17 +88,17 @@ trace_gemm_tc_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, con
     const u64 q = moduli[l];
     const ulonglong2 mu = mu_tab[l];
 
-    stage_digits<ND, false>(sA, Ar + base, 0, q);
-    stage_digits<ND, false>(sA, Ai + base, TN, q);
+    stage_digits<ND, false, TR>(sA, Ar + base, 0, q);
+    stage_digits<ND, false, TR>(sA, Ai + base, TN, q);
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {              // 0: Cr = Ar Br + Ai (q - Bi);  1: Ci = Ar Bi + Ai Br
         if (half) __syncthreads();                      // every warp is done with the first half's B'
         if (half == 0) {
-            stage_digits<ND, false>(sB, Bpr + base, 0, q);
-            stage_digits<ND, true>(sB, Bpi + base, TN, q);
+            stage_digits<ND, false, TR>(sB, Bpr + base, 0, q);
+            stage_digits<ND, true, TR>(sB, Bpi + base, TN, q);
         } else {
-            stage_digits<ND, false>(sB, Bpi + base, 0, q);
-            stage_digits<ND, false>(sB, Bpr + base, TN, q);
+            stage_digits<ND, false, TR>(sB, Bpi + base, 0, q);
+            stage_digits<ND, false, TR>(sB, Bpr + base, TN, q);
         }
         __syncthreads();
         u64* __restrict__ C = (half ? Ci : Cr) + base;
@@ -151,17 +171,13 @@ trace_gemm_tc_kernel(const u64* __restrict__ Ar, const u64* __restrict__ Ai, con
     }
 }
 
-template <int ND>
+template <int ND, bool TR>
 cudaError_t launch_trace_nd(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci, const u64* moduli,
                             const ulonglong2* mu, const LimbList& ll, int batch, cudaStream_t st) {
     constexpr int smem = 2 * ND * TN * TRS;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(trace_gemm_tc_kernel<ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return e;
-        attr = true;
-    }
-    trace_gemm_tc_kernel<ND><<<(unsigned)(batch * ll.cnt), TTH, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, 6);
+    cudaError_t e = cudaFuncSetAttribute(trace_gemm_tc_kernel<ND, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    trace_gemm_tc_kernel<ND, TR><<<(unsigned)(batch * ll.cnt), TTH, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, 6);
     return cudaGetLastError();
 }
 }  // namespace
@@ -176,16 +192,21 @@ bool trace_gemm_tc_eligible(int n, int limbs, const int* h_ndig) {
 
 cudaError_t trace_gemm_tc_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
                                  const u64* moduli, const ulonglong2* mu, const int* h_ndig, int limbs, int batch,
-                                 cudaStream_t st) {
+                                 cudaStream_t st, int transposed) {
     cudaError_t e = cudaSuccess;
     for (int nd = 4; nd <= 6 && e == cudaSuccess; ++nd) {       // one launch per digit count (<= 4 digits run as 4)
         LimbList ll; ll.cnt = 0; ll.limbs = limbs;
         for (int l = 0; l < limbs; ++l)
             if ((h_ndig[l] <= 4 ? 4 : h_ndig[l]) == nd) ll.l[ll.cnt++] = (unsigned char)l;
         if (!ll.cnt) continue;
-        e = nd == 4 ? launch_trace_nd<4>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
-          : nd == 5 ? launch_trace_nd<5>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
-                    : launch_trace_nd<6>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st);
+        if (transposed)
+            e = nd == 4 ? launch_trace_nd<4, true>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
+              : nd == 5 ? launch_trace_nd<5, true>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
+                        : launch_trace_nd<6, true>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st);
+        else
+            e = nd == 4 ? launch_trace_nd<4, false>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
+              : nd == 5 ? launch_trace_nd<5, false>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st)
+                        : launch_trace_nd<6, false>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, ll, batch, st);
     }
     return e;
 }

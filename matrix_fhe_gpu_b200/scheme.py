@@ -71,6 +71,12 @@ def _L():
         "mfhe_trace_map": [_vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_trace_gemm": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_trace_rescale": [_vp, _vp, _vp, _ci, _u64, _u64, _u64, _vp],
+        "mfhe_trace_map_x": [_vp, _vp, _vp, _vp, _vp, _ci, _vp],
+        "mfhe_trace_gemm_ty": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ci, _vp],
+        "mfhe_transpose": [_vp, _vp, _vp, C.c_size_t, _vp],
+        "mfhe_trace_rescale_limbs": [_vp, _vp, _vp, _ci, C.POINTER(_u64), _vp],
+        "mfhe_ct_matmul": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
+        "mfhe_ct_matmul_decrypt": [_vp, _vp, _vp, _vp, _vp, _vp],
         "mfhe_gl_perm_tables": [_ci, _vp, _vp],
         "mfhe_apply_gl_perm": [_vp, _vp, _ci, _ci, _ci, _ci, _vp],
         "mfhe_bconv_plan_create": [_ci, C.POINTER(_u64), _ci, C.POINTER(_u64), C.POINTER(_vp)],
@@ -366,6 +372,71 @@ class Context:
     def rescale_by_delta(self, Cr, Ci, inv0, inv1, inv2, batch=1):
         check(_L().mfhe_trace_rescale(self._h, _dev_ptr(Cr), _dev_ptr(Ci), batch, inv0, inv1, inv2, _stream_handle()))
         return Cr, Ci
+
+
+    # -- encrypted matrix product (include/mfhe.h) -----------------------------------------------
+    def trace_map_x(self, Br, Bi, batch=None):
+        import torch
+        batch = self.phi if batch is None else batch
+        o = [torch.empty_like(Br), torch.empty_like(Bi)]
+        check(_L().mfhe_trace_map_x(self._h, _dev_ptr(Br), _dev_ptr(Bi), _dev_ptr(o[0]), _dev_ptr(o[1]), batch, _stream_handle()))
+        return o
+
+    def trace_gemm_ty(self, Ur, Ui, Vr, Vi, batch=None):
+        import torch
+        batch = self.phi if batch is None else batch
+        o = [torch.empty_like(Ur), torch.empty_like(Ui)]
+        check(_L().mfhe_trace_gemm_ty(self._h, _dev_ptr(Ur), _dev_ptr(Ui), _dev_ptr(Vr), _dev_ptr(Vi), _dev_ptr(o[0]),
+                                      _dev_ptr(o[1]), batch, _stream_handle()))
+        return o
+
+    def transpose(self, x):
+        import torch
+        o = torch.empty_like(x)
+        check(_L().mfhe_transpose(self._h, _dev_ptr(x), _dev_ptr(o), x.numel() // self.n2, _stream_handle()))
+        return o
+
+    def rescale_limbs(self, Cr, Ci, inv, batch=None):
+        batch = self.phi if batch is None else batch
+        arr = (_u64 * self.L)(*[int(v) for v in inv])
+        check(_L().mfhe_trace_rescale_limbs(self._h, _dev_ptr(Cr), _dev_ptr(Ci), batch, arr, _stream_handle()))
+        return Cr, Ci
+
+    def ct_matmul(self, cu_re, cu_im, cv_re, cv_im):
+        """The four component GEMMs of ct_U x ct_V' (V' = trace_map_x of the encoded V, then encrypted): 8 poly sets."""
+        o = self._new(8 * self.T, like=cu_re)
+        check(_L().mfhe_ct_matmul(self._h, _dev_ptr(cu_re), _dev_ptr(cu_im), _dev_ptr(cv_re), _dev_ptr(cv_im), _dev_ptr(o),
+                                  _stream_handle()))
+        return o
+
+    def ct_matmul_decrypt(self, prod, sk):
+        """Consumes `prod`; returns evals (re, im) [w][l][z][x] of n * sum_y U[y][x] V'[y][z]."""
+        o = [self._new(self.T, like=prod), self._new(self.T, like=prod)]
+        check(_L().mfhe_ct_matmul_decrypt(self._h, _dev_ptr(prod), _dev_ptr(sk), _dev_ptr(o[0]), _dev_ptr(o[1]), _stream_handle()))
+        return o
+
+    def conj_lane(self):
+        """l -> l' with exp[l'] = -exp[l] mod p (see encrypted_matmul)."""
+        import numpy as np
+        e = [((a * self.f + 3 * b) % self.p) for a in (1, 2) for b in range(1, self.f)]      # k_wntt_exp, HE.cu:72-105
+        pos = {v: i for i, v in enumerate(e)}
+        return np.asarray([pos[(self.p - v) % self.p] for v in e], dtype=np.int64)
+
+    def encrypted_matmul(self, U, V, sk):
+        """Encrypted matrix product driver: per lane l, R_l = V_l^H . U_l for complex n x n matrices U, V ([phi][n][n]
+        complex128 device tensors): encode -> (V: lane permutation + X twist) -> encrypt both -> four GEMMs on the
+        ciphertext components (tensor cores) -> 4-component decrypt -> decode.  Returns R [phi][n][n] complex128."""
+        import torch
+        cl = torch.from_numpy(self.conj_lane()).to(U.device)
+        ur, ui = self.encode_to_wntt_eval(U.reshape(-1))
+        vr, vi = self.encode_to_wntt_eval(V.reshape(self.phi, -1)[cl].reshape(-1))
+        vpr, vpi = self.trace_map_x(vr, vi)
+        cu = self.encrypt_pair(ur, ui, sk)
+        cv = self.encrypt_pair(vpr, vpi, sk)
+        prod = self.ct_matmul(cu[0], cu[1], cv[0], cv[1])
+        pr, pi = self.ct_matmul_decrypt(prod, sk)
+        out = self.decode_eval_pair(pr, pi, MATRIX)            # divides by delta once; the product carries delta^2
+        return (out / self.delta).reshape(self.phi, self.n, self.n)
 
 
 def gl_perm_tables(n):

@@ -250,6 +250,10 @@ def _scheme_lib():
         "mfo_trace_map": [vp, _p64, _p64, _p64, _p64, ci],
         "mfo_trace_gemm": [vp, _p64, _p64, _p64, _p64, _p64, _p64, ci],
         "mfo_trace_rescale": [vp, _p64, _p64, ci, u64, u64, u64],
+        "mfo_trace_map_x": [vp, _p64, _p64, _p64, _p64, ci],
+        "mfo_trace_gemm_ty": [vp, _p64, _p64, _p64, _p64, _p64, _p64, ci],
+        "mfo_ct_matmul": [vp, _p64, _p64, _p64, _p64, _p64],
+        "mfo_ct_matmul_decrypt": [vp, _p64, _p64, _p64, _p64],
         "mfo_bconv": [_p64, _p64, C.c_size_t, ci, _p64, ci, _p64],
     }
     for name, args in sig.items():
@@ -464,6 +468,27 @@ class SchemeCtx:
     def trace_gemm(self, Ar, Ai, Bpr, Bpi, batch):
         o = [np.zeros_like(Ar), np.zeros_like(Ai)]
         self._L.mfo_trace_gemm(self._h, Ar, Ai, Bpr, Bpi, o[0], o[1], batch); return o
+
+    # -- encrypted matrix product --------------------------------------------------
+    def trace_map_x(self, Br, Bi, batch):
+        o = [np.zeros_like(Br), np.zeros_like(Bi)]; self._L.mfo_trace_map_x(self._h, Br, Bi, o[0], o[1], batch); return o
+
+    def trace_gemm_ty(self, Ur, Ui, Vr, Vi, batch):
+        o = [np.zeros_like(Ur), np.zeros_like(Ui)]
+        self._L.mfo_trace_gemm_ty(self._h, Ur, Ui, Vr, Vi, o[0], o[1], batch); return o
+
+    def ct_matmul(self, cu_re, cu_im, cv_re, cv_im):
+        o = self._u(8 * self.T); self._L.mfo_ct_matmul(self._h, cu_re, cu_im, cv_re, cv_im, o); return o
+
+    def ct_matmul_decrypt(self, prod, sk):
+        o = [self._u(self.T), self._u(self.T)]; self._L.mfo_ct_matmul_decrypt(self._h, prod, sk, o[0], o[1]); return o
+
+    def conj_lane(self):
+        """Involution l -> l' of the W lanes with exp[l'] = -exp[l] mod p: coefficient-wise conjugation of an encoded
+        plaintext conjugates the slot values of lane l' into lane l (the W evaluation points are complex)."""
+        e = [int(v) for v in self.wexp()]
+        pos = {v: i for i, v in enumerate(e)}
+        return np.asarray([pos[(self.p - v) % self.p] for v in e], dtype=np.int64)
 
     def trace_rescale(self, Cr, Ci, batch, inv0, inv1, inv2):
         Cr, Ci = Cr.copy(), Ci.copy(); self._L.mfo_trace_rescale(self._h, Cr, Ci, batch, inv0, inv1, inv2); return Cr, Ci

@@ -397,6 +397,89 @@ void mfo_trace_rescale(const mfo_ctx *c, uint64_t *Cr, uint64_t *Ci, int batch, 
     }
 }
 
+/* ---- encrypted matrix product: SURVEY 8(f) rank 1 (no reference caller exists; restated from the definitions the
+ * reference's pieces give: trace.cu:30-62 for the twist, trace.cu:77-120 for the Gaussian-integer GEMM and its factor n,
+ * HE.cu:1553-1601 for "m = b + a (*) s" as the meaning of a ciphertext).  Operands: poly sets [w][l][y][x]. ---------- */
+/* the map of trace.cu:30-62 with the twisted index being x (fast): B'[y][(-x) mod n] = conj(B[y][x]) * (x == 0 ? 1 : -i) */
+void mfo_trace_map_x(const mfo_ctx *c, const uint64_t *Br, const uint64_t *Bi, uint64_t *Bpr, uint64_t *Bpi, int batch) {
+    const int n = c->n; const size_t n2 = (size_t)n * n, L = (size_t)c->L;
+    for (size_t b = 0; b < (size_t)batch; ++b)
+        for (size_t l = 0; l < L; ++l) {
+            uint64_t q = c->moduli[l]; size_t base = (b * L + l) * n2;
+            for (int y = 0; y < n; ++y)
+                for (int x = 0; x < n; ++x) {
+                    size_t src = base + (size_t)y * n + x, dst = base + (size_t)y * n + ((n - x) & (n - 1));
+                    uint64_t a = Br[src], bb = Bi[src];
+                    if (x == 0) { Bpr[dst] = a; Bpi[dst] = neg_mod(bb, q); }
+                    else { Bpr[dst] = neg_mod(bb, q); Bpi[dst] = neg_mod(a, q); }
+                }
+        }
+}
+/* D[x][z] = n * sum_y U[y][x] * V[y][z]  over Z_q[i], per (batch, limb) */
+void mfo_trace_gemm_ty(const mfo_ctx *c, const uint64_t *Ur, const uint64_t *Ui, const uint64_t *Vr, const uint64_t *Vi,
+                       uint64_t *Dr, uint64_t *Di, int batch) {
+    const int n = c->n; const size_t n2 = (size_t)n * n, L = (size_t)c->L;
+#pragma omp parallel for schedule(static)
+    for (long bl = 0; bl < (long)((size_t)batch * L); ++bl) {
+        size_t l = (size_t)bl % L, base = (size_t)bl * n2;
+        uint64_t q = c->moduli[l], nm = (uint64_t)n % q;
+        for (int x = 0; x < n; ++x)
+            for (int z = 0; z < n; ++z) {
+                uint64_t sr = 0, si = 0;
+                for (int y = 0; y < n; ++y) {
+                    uint64_t ur = Ur[base + (size_t)y * n + x], ui = Ui[base + (size_t)y * n + x];
+                    uint64_t vr = Vr[base + (size_t)y * n + z], vi = Vi[base + (size_t)y * n + z];
+                    sr = mfo_addmod(sr, mfo_submod(mfo_mulmod(ur, vr, q), mfo_mulmod(ui, vi, q), q), q);
+                    si = mfo_addmod(si, mfo_addmod(mfo_mulmod(ur, vi, q), mfo_mulmod(ui, vr, q), q), q);
+                }
+                Dr[base + (size_t)x * n + z] = mfo_mulmod(sr, nm, q);
+                Di[base + (size_t)x * n + z] = mfo_mulmod(si, nm, q);
+            }
+    }
+}
+/* out = 8 poly sets [bb re, im | ab re, im | ba re, im | aa re, im] */
+void mfo_ct_matmul(const mfo_ctx *c, const uint64_t *ctU_re, const uint64_t *ctU_im, const uint64_t *ctV_re,
+                   const uint64_t *ctV_im, uint64_t *out) {
+    const size_t T = (size_t)c->phi * c->L * c->n * c->n;
+    for (int k = 0; k < 4; ++k) {
+        size_t uo = (k & 1) ? T : 0, vo = (k & 2) ? T : 0;
+        mfo_trace_gemm_ty(c, ctU_re + uo, ctU_im + uo, ctV_re + vo, ctV_im + vo, out + (size_t)(2 * k) * T,
+                          out + (size_t)(2 * k + 1) * T, c->phi);
+    }
+}
+/* o = m + a (*) s along the fast index of matrix-major data, s = key [w][l][x] in NTT form (HE.cu:1579-1590) */
+static void rows_add_as(const mfo_ctx *c, const uint64_t *m, const uint64_t *a, const uint64_t *sk, uint64_t *o) {
+    const size_t n = (size_t)c->n, L = (size_t)c->L, rows = (size_t)c->phi * L * n;
+#pragma omp parallel for schedule(static)
+    for (long r = 0; r < (long)rows; ++r) {
+        size_t wl = (size_t)r / n, l = wl % L;
+        uint64_t q = c->moduli[l], t[256];
+        memcpy(t, a + (size_t)r * n, n * 8);
+        mfo_negacyclic_forward(t, c->logn, q, c->tw + l * n, c->tws + l * n);
+        for (size_t x = 0; x < n; ++x) t[x] = mfo_mulmod(t[x], sk[wl * n + x], q);
+        mfo_negacyclic_inverse(t, c->logn, q, c->itw + l * n, c->itws + l * n, c->ninv[l], c->ninvs[l]);
+        for (size_t x = 0; x < n; ++x) o[(size_t)r * n + x] = mfo_addmod(m[(size_t)r * n + x], t[x], q);
+    }
+}
+static void transpose_set(const mfo_ctx *c, const uint64_t *in, uint64_t *out) {
+    const size_t n = (size_t)c->n, mats = (size_t)c->phi * c->L;
+    for (size_t mtx = 0; mtx < mats; ++mtx)
+        for (size_t i = 0; i < n; ++i)
+            for (size_t j = 0; j < n; ++j) out[(mtx * n + j) * n + i] = in[(mtx * n + i) * n + j];
+}
+/* D_bb + D_ab (*)_x s + D_ba (*)_z s + D_aa (*)_x s (*)_z s, returned as [w][l][z][x] */
+void mfo_ct_matmul_decrypt(const mfo_ctx *c, const uint64_t *prod, const uint64_t *sk, uint64_t *out_re, uint64_t *out_im) {
+    const size_t T = (size_t)c->phi * c->L * c->n * c->n;
+    uint64_t *acc = (uint64_t *)malloc(T * 8), *e = (uint64_t *)malloc(T * 8), *at = (uint64_t *)malloc(T * 8), *et = (uint64_t *)malloc(T * 8);
+    for (int part = 0; part < 2; ++part) {
+        rows_add_as(c, prod + (size_t)(0 + part) * T, prod + (size_t)(4 + part) * T, sk, acc);   /* bb + ba (*)_z s */
+        rows_add_as(c, prod + (size_t)(2 + part) * T, prod + (size_t)(6 + part) * T, sk, e);     /* ab + aa (*)_z s */
+        transpose_set(c, acc, at); transpose_set(c, e, et);
+        rows_add_as(c, at, et, sk, part ? out_im : out_re);
+    }
+    free(acc); free(e); free(at); free(et);
+}
+
 /* ---- Phantom bConv_BEHZ: ph/src/rns_bconv.cu:22-29, 109-131, 212-229 ------------------------------ */
 void mfo_bconv(const uint64_t *in, uint64_t *out, size_t N, int L_in, const uint64_t *q_in, int L_out, const uint64_t *p_out) {
     uint64_t *qhat_inv = (uint64_t *)malloc((size_t)L_in * 8), *qhat_mod_p = (uint64_t *)malloc((size_t)L_in * L_out * 8);

@@ -137,6 +137,13 @@ void mfo_trace_map(const mfo_ctx *c, const uint64_t *Br, const uint64_t *Bi, uin
 void mfo_trace_gemm(const mfo_ctx *c, const uint64_t *Ar, const uint64_t *Ai, const uint64_t *Bpr, const uint64_t *Bpi,
                     uint64_t *Cr, uint64_t *Ci, int batch);
 void mfo_trace_rescale(const mfo_ctx *c, uint64_t *Cr, uint64_t *Ci, int batch, uint64_t inv0, uint64_t inv1, uint64_t inv2);
+/* encrypted matrix product */
+void mfo_trace_map_x(const mfo_ctx *c, const uint64_t *Br, const uint64_t *Bi, uint64_t *Bpr, uint64_t *Bpi, int batch);
+void mfo_trace_gemm_ty(const mfo_ctx *c, const uint64_t *Ur, const uint64_t *Ui, const uint64_t *Vr, const uint64_t *Vi,
+                       uint64_t *Dr, uint64_t *Di, int batch);
+void mfo_ct_matmul(const mfo_ctx *c, const uint64_t *ctU_re, const uint64_t *ctU_im, const uint64_t *ctV_re,
+                   const uint64_t *ctV_im, uint64_t *out);
+void mfo_ct_matmul_decrypt(const mfo_ctx *c, const uint64_t *prod, const uint64_t *sk, uint64_t *out_re, uint64_t *out_im);
 
 /* ---- Phantom base conversion: ph/src/rns_bconv.cu:22-29,109-131,212-229 ------------------ */
 /* in [L_in][N], out [L_out][N];  qhat_inv[i] = (Q/q_i)^-1 mod q_i, qhat_mod_p[j][i] = Q/q_i mod p_j */

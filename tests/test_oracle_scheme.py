@@ -233,3 +233,68 @@ def test_bconv_definitional():
         y = [(int(x[i, d]) * pow(Q // q[i], -1, q[i])) % q[i] for i in range(l_in)]
         for j in range(l_out):
             assert int(out[j, d]) == sum(y[i] * ((Q // q[i]) % p[j]) for i in range(l_in)) % p[j]
+
+
+# ---- encrypted matrix product: the oracle's restatement against plaintext linear algebra ----
+def _matmul_ctx():
+    # n = 16, p = 15 (phi = 8), five ~45-bit limbs: Q ~ 2^225 holds delta^2 * n * phi * |c|^2 with room to spare
+    mods = O.primes_congruent_one(960, 45, 5)
+    return O.SchemeCtx(16, 5, mods, 2.0 ** 30)
+
+
+def test_conj_lane_is_an_involution_matching_the_exponents():
+    for o in (_matmul_ctx(), O.SchemeCtx(moduli=O.REF_MODULI[:1])):
+        cl, e = o.conj_lane(), [int(v) for v in o.wexp()]
+        assert (cl[cl] == np.arange(o.phi)).all()
+        assert all((e[i] + e[int(cl[i])]) % o.p == 0 for i in range(o.phi))
+
+
+def test_trace_map_x_is_the_reference_map_on_transposed_matrices():
+    """mfo_trace_map_x twists the fast index; on transposed matrices it is exactly trace.cu:30-62 (which twists the slow one)."""
+    o = _matmul_ctx()
+    rng = np.random.default_rng(2)
+    batch = 3
+    q = np.asarray(o.moduli, dtype=np.uint64).reshape(1, -1, 1, 1)
+    Br = rng.integers(0, 2 ** 62, size=(batch, o.L, o.n, o.n), dtype=np.uint64) % q
+    Bi = rng.integers(0, 2 ** 62, size=(batch, o.L, o.n, o.n), dtype=np.uint64) % q
+    xr, xi = o.trace_map_x(Br.reshape(-1), Bi.reshape(-1), batch)
+    tr = lambda a: np.ascontiguousarray(a.reshape(batch, o.L, o.n, o.n).transpose(0, 1, 3, 2)).reshape(-1)
+    rr, ri = o.trace_map(tr(Br), tr(Bi), batch)
+    assert (tr(rr) == xr).all() and (tr(ri) == xi).all()
+    # and trace_gemm_ty == trace_gemm on transposed operands
+    Ar = rng.integers(0, 2 ** 62, size=(batch, o.L, o.n, o.n), dtype=np.uint64) % q
+    Ai = rng.integers(0, 2 ** 62, size=(batch, o.L, o.n, o.n), dtype=np.uint64) % q
+    dr, di = o.trace_gemm_ty(Ar.reshape(-1), Ai.reshape(-1), Br.reshape(-1), Bi.reshape(-1), batch)
+    cr, ci = o.trace_gemm(tr(Ar), tr(Ai), tr(Br), tr(Bi), batch)
+    assert (dr == cr).all() and (di == ci).all()
+
+
+def test_encrypted_matmul_decrypts_to_the_plaintext_product():
+    """encode -> (V: conjugate-lane permutation, X twist) -> encrypt -> 4 component GEMMs -> 4-term decrypt -> decode
+    == V^H U per lane (the factor n of the trace GEMM is part of the identity: sum_a xi_a^(r-r') = n [r = r']).
+    Tolerance: the product of two encodings carries delta^2; each factor's quantisation error is <= 1/2 and the gaussian
+    errors ~ 3.2 per W-coefficient, so the relative error is ~ (phi n)^(1/2) * 4 / (delta * |m|) ~ 2^-24 at delta = 2^30:
+    asserted against the north-star bound 2^-20 * max|entry|."""
+    o = _matmul_ctx()
+    rng = np.random.default_rng(7)
+    U = (rng.standard_normal((o.phi, o.n, o.n)) + 1j * rng.standard_normal((o.phi, o.n, o.n))) * 3
+    V = (rng.standard_normal((o.phi, o.n, o.n)) + 1j * rng.standard_normal((o.phi, o.n, o.n))) * 3
+    cl = o.conj_lane()
+    ur, ui = o.encode(U.reshape(-1))
+    vr, vi = o.encode(V[cl].reshape(-1))
+    vpr, vpi = o.trace_map_x(vr, vi, o.phi)
+    sk = o.keygen()
+    cur, cui = o.encrypt_pair(ur, ui, sk)
+    cvr, cvi = o.encrypt_pair(vpr, vpi, sk)
+    prod = o.ct_matmul(cur, cui, cvr, cvi)
+    pr, pi = o.ct_matmul_decrypt(prod, sk)
+    out = o.decode_eval_pair(o.matrix_to_poly(pr), o.matrix_to_poly(pi)).reshape(o.phi, o.n, o.n) / o.delta
+    want = np.einsum("lab,lac->lbc", V.conj(), U)          # V^H U per lane
+    err = np.abs(out - want).max()
+    print(f"encrypted matmul (oracle, n=16 phi=8): max_err {err:.3e} on entries up to {np.abs(want).max():.1f}")
+    assert err <= 2.0 ** -20 * np.abs(want).max()
+    # the plaintext side of the same identity, no encryption: n * U^T V' decoded
+    dr, di = o.trace_gemm_ty(ur, ui, vpr, vpi, o.phi)
+    tr = lambda a: np.ascontiguousarray(a.reshape(o.phi, o.L, o.n, o.n).transpose(0, 1, 3, 2)).reshape(-1)
+    plain = o.decode_eval_pair(o.matrix_to_poly(tr(dr)), o.matrix_to_poly(tr(di))).reshape(o.phi, o.n, o.n) / o.delta
+    assert np.abs(plain - want).max() <= 2.0 ** -24 * np.abs(want).max()
