@@ -49,6 +49,7 @@ const char *mfhe_version(void);
  * Flat RNS negacyclic NTT over [batch][L][N] u64 (family A of SURVEY.md).
  * ------------------------------------------------------------------------ */
 typedef struct mfhe_ntt_plan mfhe_ntt_plan;
+typedef struct mfhe_bconv_plan mfhe_bconv_plan;      /* base conversion plan, declared below */
 
 /* X-axis conventions of the reference */
 #define MFHE_NTT_PHANTOM_NEGACYCLIC 0 /* X^N + 1, natural in -> bit-reversed out
@@ -220,6 +221,14 @@ int mfhe_decode_lane_from_rns_eval(mfhe_ctx *ctx, const uint64_t *d_re, const ui
 /* ---- samplers, keys, encrypt / decrypt (src/core/HE.cu) ------------------------------------------ */
 /* uniform_random_kernel :564-578, gaussian_noise_kernel :590-627 (MATRIX, W-coeff),
  * ternary_secret_kernel :690-713 ([w][limb][x]) */
+/* Sampler option.  mode 0 (default): the reference's index-hash "samplers" (HE.cu:564-627, 690-713),
+ * reproducible and NOT encryption randomness -- the parity mode.  mode 1: Philox4x32-10 keyed by the 128-bit `seed`
+ * (uniform by 128-bit reduction, discrete gaussian sigma = 3.2 by a 64-bit cumulative table, uniform ternary key), every
+ * sampled array under a fresh draw number; affects mfhe_sample_*, mfhe_keygen, mfhe_encrypt*, mfhe_encode_encrypt_pair.
+ * Setting the mode resets the draw number (same seed => same streams: testable against the oracle). */
+int mfhe_ctx_set_sampler(mfhe_ctx *ctx, int mode, const uint64_t seed[2]);
+/* the 83-entry cumulative table of the discrete gaussian (z = -41 .. 41), for cross-checks */
+int mfhe_sampler_cdt(uint64_t *h_out, int count);
 int mfhe_sample_uniform(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
 int mfhe_sample_gaussian(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
 int mfhe_sample_ternary(mfhe_ctx *ctx, uint64_t *d_out, void *stream);
@@ -282,14 +291,30 @@ int mfhe_ct_matmul(mfhe_ctx *ctx, const uint64_t *d_ctU_re, const uint64_t *d_ct
 /* decrypts the 4-component product (d_prod is consumed as scratch); out = evals [w][l][z][x] of n * sum_y U V' */
 int mfhe_ct_matmul_decrypt(mfhe_ctx *ctx, uint64_t *d_prod, const uint64_t *d_sk, uint64_t *d_out_re, uint64_t *d_out_im, void *stream);
 
+/* ---- mod-up / mod-down with an auxiliary base P (config.h:22,46-52 reserves P_MODULI, Phantom:
+ * ph/src/ntt/ntt_modup.cu, ntt_moddown.cu, ph/src/rns_bconv.cu:530-830).  `qp` is a flat plan whose limbs are Q then P.
+ * mod-up:   d_x [batch][LQ][N] COEFFICIENT form over Q -> d_out [batch][LQ+LP][N] NTT form over Q u P (q_to_p: Q -> P).
+ * mod-down: d_x [batch][LQ+LP][N] NTT form -> d_out [batch][LQ][N] NTT form, (x - [x]_P) / P up to the base conversion's
+ *           multiple-of-P slack (|error| < LP); p_to_q: P -> Q; d_scratch: batch * LP * N words. ---- */
+int mfhe_modup(const mfhe_ntt_plan *qp, const mfhe_bconv_plan *q_to_p, const uint64_t *d_x, uint64_t *d_out, size_t batch,
+               void *stream);
+int mfhe_moddown(const mfhe_ntt_plan *qp, const mfhe_bconv_plan *p_to_q, const uint64_t *d_x, uint64_t *d_out,
+                 uint64_t *d_scratch, size_t batch, void *stream);
+
+/* ---- RNS rescale of the matrix scheme (the reference reserves the chain -- delta = 2^35 next to
+ * ten 35-bit primes, config.h:25-44 -- and ships only rescale_by_delta_rns, trace.cu:132-161, a multiplication by constants).
+ * X' = (X - [X]_q_last) / q_last on the integer W-coefficients; in [w][L][n^2] -> out [w][L-1][n^2] (a poly set of a context
+ * created on moduli[0 .. L-2]).  Works on plaintext evals and on each half / component of a ciphertext alike. */
+int mfhe_rescale_last(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, void *stream);
+
 int mfhe_gl_perm_tables(int n, uint32_t *h_perm, uint32_t *h_inv_perm);
 int mfhe_apply_gl_perm(const uint64_t *d_in, uint64_t *d_out, int limbs, int batch_count, int n, int inverse, void *stream);
 
 /* ---- RNS base conversion (Phantom DBaseConverter::bConv_BEHZ, ph/src/rns_bconv.cu:212-229) -------- */
-typedef struct mfhe_bconv_plan mfhe_bconv_plan;
 int mfhe_bconv_plan_create(int l_in, const uint64_t *q_in, int l_out, const uint64_t *p_out, mfhe_bconv_plan **out);
 void mfhe_bconv_plan_destroy(mfhe_bconv_plan *plan);
 /* d_in [batch][l_in][N] -> d_out [batch][l_out][N] */
+int mfhe_bconv_plan_sizes(const mfhe_bconv_plan *plan, int *l_in, int *l_out);
 int mfhe_bconv(const mfhe_bconv_plan *plan, const uint64_t *d_in, uint64_t *d_out, size_t N, size_t batch, void *stream);
 /* limb-sharded form: this rank holds input limbs [in_start, in_start+in_count); writes the partial
  * sums mod p_j of ALL output limbs, each < p_j, to d_partial [batch][l_out][N]; summing the ranks'

@@ -176,6 +176,13 @@ extern "C" int mfhe_bconv_plan_create(int l_in, const uint64_t* q_in, int l_out,
     if (qmax >= (1ull << 61) || pmax >= (1ull << 61) || bound >= 3.4028236692093846e38L) {
         delete b; return fail(MFHE_EUNSUPPORTED, "bconv_plan_create: l_in * q * p must stay below 2^128 and moduli below 2^61");
     }
+    // the output moduli feed make_barrett1 (shifts by k - 2 and 66 - k) and the floor(2^128 / p) constants: odd, >= 2^3,
+    // pairwise distinct
+    for (int j = 0; j < l_out; ++j) {
+        if (p_out[j] < 8 || !(p_out[j] & 1)) { delete b; return fail(MFHE_EINVAL, "bconv_plan_create: output moduli must be odd and >= 8"); }
+        for (int k = 0; k < j; ++k)
+            if (p_out[k] == p_out[j]) { delete b; return fail(MFHE_EINVAL, "bconv_plan_create: output moduli must be distinct"); }
+    }
     for (int i = 0; i < l_in; ++i) {
         const uint64_t q = q_in[i];
         if (q < 3 || !(q & 1)) { delete b; return fail(MFHE_EINVAL, "bconv_plan_create: moduli must be odd"); }
@@ -256,6 +263,11 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
 #undef MFHE_BCONV_LAUNCH
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
+}
+extern "C" int mfhe_bconv_plan_sizes(const mfhe_bconv_plan* b, int* l_in, int* l_out) {
+    if (!b || !l_in || !l_out) return fail(MFHE_EINVAL, "bconv_plan_sizes: NULL argument");
+    *l_in = b->l_in; *l_out = b->l_out;
+    return MFHE_OK;
 }
 extern "C" int mfhe_bconv(const mfhe_bconv_plan* b, const uint64_t* in, uint64_t* out, size_t N, size_t batch, void* s) {
     return bconv_run(b, in, 0, b ? b->l_in : 0, out, N, batch, s, "bconv");

@@ -207,8 +207,9 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     UP(c->d_crt_Q, crt.Q); UP(c->d_crt_Qhalf, crt.Qhalf); UP(c->d_crt_M, crt.M); UP(c->d_crt_inv, crt.inv);
 #undef UP
     if (e == cudaSuccess) {
-        // scratch: 4 poly sets + 4 complex lane sets (decrypt_decode is the largest consumer)
-        const size_t need = 4 * c->T() * 8 + 4 * phi * nn * 16 + (1 << 20);
+        // scratch: 6 poly sets + 4 complex lane sets (largest consumers: decrypt_decode with 4 + 4, and encrypt_pair under
+        // the sound sampler with 3 drawn arrays + 2 transformed errors + 1 materialised source)
+        const size_t need = 6 * c->T() * 8 + 4 * phi * nn * 16 + (1 << 20);
         c->arena_bytes = std::max(need, p->arena_bytes);
         e = cudaMalloc((void**)&c->arena, c->arena_bytes);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->arena_ev, cudaEventDisableTiming);
@@ -438,9 +439,26 @@ extern "C" int mfhe_decode_lane_from_rns_eval(mfhe_ctx* c, const uint64_t* re, c
 }
 
 // ---- samplers, keys -------------------------------------------------------------------------------------
+// draws one array in the context's sampler mode; the sound mode consumes one draw number per array
+static cudaError_t draw_array(mfhe_ctx* c, int kind, u64* out, cudaStream_t st) {
+    if (c->sampler_mode == 0) return sample_launch(kind, out, c->d_moduli, c->d_mu, c->n, c->L, c->phi, st);
+    return sound_sample_launch(kind, out, c->d_moduli, c->d_mu, c->n, c->L, c->phi, c->seed[0], c->seed[1], c->draw++, st);
+}
 static int sample(mfhe_ctx* c, int kind, uint64_t* out, void* s, const char* who) {
     if (!c || !out) return fail(MFHE_EINVAL, std::string(who) + ": NULL argument");
-    return done(sample_launch(kind, (u64*)out, c->d_moduli, c->d_mu, c->n, c->L, c->phi, S(s)), who);
+    return done(draw_array(c, kind, (u64*)out, S(s)), who);
+}
+extern "C" int mfhe_ctx_set_sampler(mfhe_ctx* c, int mode, const uint64_t* seed) {
+    if (!c || (mode != 0 && mode != 1) || (mode == 1 && !seed)) return fail(MFHE_EINVAL, "ctx_set_sampler: bad argument");
+    std::lock_guard<std::mutex> lk(c->arena_mu);
+    c->sampler_mode = mode; c->draw = 0;
+    c->seed[0] = mode ? seed[0] : 0; c->seed[1] = mode ? seed[1] : 0;
+    return MFHE_OK;
+}
+extern "C" int mfhe_sampler_cdt(uint64_t* h_out, int count) {
+    if (!h_out || count != 83) return fail(MFHE_EINVAL, "sampler_cdt: the table has 83 entries");
+    sound_cdt_copy((u64*)h_out);
+    return MFHE_OK;
 }
 extern "C" int mfhe_sample_uniform(mfhe_ctx* c, uint64_t* out, void* s) { return sample(c, 0, out, s, "sample_uniform"); }
 extern "C" int mfhe_sample_gaussian(mfhe_ctx* c, uint64_t* out, void* s) { return sample(c, 1, out, s, "sample_gaussian"); }
@@ -452,7 +470,7 @@ extern "C" int mfhe_keygen(mfhe_ctx* c, uint64_t* sk, void* s) {
     const size_t total = (size_t)c->phi * c->L * c->n;
     u64* sc = (u64*)c->take(total * 8);
     if (!sc) return fail(MFHE_ENOMEM, "keygen: arena too small");
-    cudaError_t e = sample_launch(2, sc, c->d_moduli, c->d_mu, c->n, c->L, c->phi, S(s));
+    cudaError_t e = draw_array(c, 2, sc, S(s));
     if (e == cudaSuccess) {
         WcrtArgs a = wcrt_args(c, false);
         a.in = sc; a.out = (u64*)sk; a.cols = c->n;
@@ -471,6 +489,20 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
     ArenaScope arena_scope(c, S(s));
     const size_t T = c->T();
     cudaStream_t st = S(s);
+    if (c->sampler_mode == 1 && a_src == kSrcUniform) {
+        // sound sampler: a and e are drawn (Philox, fresh draw numbers) into scratch and enter as memory sources; the
+        // error of the im ciphertext is its OWN draw (the reference reuses one stream for both, HE.cu:1516-1517)
+        u64* da = (u64*)c->take(T * 8);
+        u64* de = (u64*)c->take(T * 8);
+        u64* de2 = ct_im ? (u64*)c->take(T * 8) : nullptr;
+        if (!da || !de || (ct_im && !de2)) return fail(MFHE_ENOMEM, std::string(who) + ": arena too small for the sound sampler");
+        cudaError_t e0 = draw_array(c, 0, da, st);
+        if (e0 == cudaSuccess) e0 = draw_array(c, 1, de, st);
+        if (e0 == cudaSuccess && ct_im) e0 = draw_array(c, 1, de2, st);
+        if (e0 != cudaSuccess) return done(e0, who);
+        // the three arrays stay live: run the memory-source body on the rest of the arena
+        a_src = kSrcMem; a_coeff = (const uint64_t*)da; e_src = kSrcMem; e_re = (const uint64_t*)de; e_im = (const uint64_t*)(ct_im ? de2 : de);
+    }
     const bool two_e = ct_im && e_src == kSrcMem && e_im != e_re;
     u64* E0 = (u64*)c->take(T * 8);
     u64* E1 = two_e ? (u64*)c->take(T * 8) : E0;
@@ -526,6 +558,13 @@ extern "C" int mfhe_encrypt_pair_with(mfhe_ctx* c, const uint64_t* m_re, const u
 extern "C" int mfhe_encode_encrypt_pair(mfhe_ctx* c, const double* msg, const uint64_t* sk, uint64_t* ct_re, uint64_t* ct_im,
                                         void* s) {
     if (!c || !msg || !sk || !ct_re || !ct_im) return fail(MFHE_EINVAL, "encode_encrypt_pair: NULL argument");
+    if (c->sampler_mode == 1) {
+        // the shared-W-CRT fusion below rests on the reference's gaussian stream; under the sound sampler the message is
+        // encoded into the b halves and encrypted in place (same result as the two calls in sequence)
+        int rc = mfhe_encode(c, msg, ct_re, ct_im, s);
+        return rc != MFHE_OK ? rc : encrypt_core(c, ct_re, ct_im, sk, kSrcUniform, nullptr, kSrcGauss, nullptr, nullptr, ct_re, ct_im, s,
+                                                 "encode_encrypt_pair");
+    }
     ArenaScope arena_scope(c, S(s));
     const size_t T = c->T(), total = (size_t)c->phi * c->n2(), lanes_bytes = total * sizeof(double2);
     double2* xy = (double2*)c->take(lanes_bytes);
@@ -694,6 +733,45 @@ extern "C" int mfhe_ct_matmul_decrypt(mfhe_ctx* c, uint64_t* prod, const uint64_
     // 4. out = (D_bb)^T + (D_ab)^T (*)_x s
     if (e == cudaSuccess) e = rows(D + 4 * T, D + 5 * T, D + 6 * T, D + 7 * T, (u64*)out_re, (u64*)out_im);
     return done(e, "ct_matmul_decrypt");
+}
+
+// ---- RNS rescale of the matrix scheme ---------------------------------------------------------
+// Divides a poly set by its last modulus q_last (~ delta: the reference's ten 35-bit primes next to delta = 2^35 are a
+// rescale chain, config.h:25-44) and drops that limb:  X' = (X - [X]_{q_last}) / q_last  on the integer W-coefficients.
+// In the W-eval domain of limb i < L-1 that is  (x_i - Wcrt_i([X]_{q_last})) * q_last^-1 mod q_i, and [X]_{q_last} (centred)
+// is the inverse W-CRT of the last limb alone: 1/L of an inverse W-CRT + (L-1)/L of a forward one (int64 source).
+// in: [w][L][n^2] evals (MATRIX layout), out: [w][L-1][n^2] -- a poly set of a context built on moduli[0 .. L-2].
+extern "C" int mfhe_rescale_last(mfhe_ctx* c, const uint64_t* in, uint64_t* out, void* s) {
+    if (!c || !in || !out || in == out) return fail(MFHE_EINVAL, "rescale_last: bad argument");
+    if (c->L < 2) return fail(MFHE_EINVAL, "rescale_last: needs at least two limbs");
+    ArenaScope arena_scope(c, S(s));
+    cudaStream_t st = S(s);
+    const int L = c->L, cols = (int)c->n2();
+    const size_t lane = (size_t)c->phi * cols;
+    u64* last = (u64*)c->take(lane * 8);
+    u64* coef = (u64*)c->take(lane * 8);
+    long long* cen = (long long*)c->take(lane * 8);
+    if (!last || !coef || !cen) return fail(MFHE_ENOMEM, "rescale_last: arena too small");
+    cudaError_t e = cudaMemcpy2DAsync(last, (size_t)cols * 8, (const u64*)in + (size_t)(L - 1) * cols, (size_t)L * cols * 8,
+                                      (size_t)cols * 8, (size_t)c->phi, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) {
+        WcrtArgs a = wcrt_args(c, true);
+        a.in = last; a.out = coef; a.limbs = 1; a.limb0 = L - 1;
+        e = wcrt_launch(a, st);
+    }
+    if (e == cudaSuccess) e = center_i64_launch(coef, cen, c->moduli[L - 1], lane, st);
+    if (e == cudaSuccess) {
+        WcrtArgs a = wcrt_args(c, false);
+        a.in = cen; a.out = (u64*)out; a.source = kSrcI64; a.limbs = L - 1; a.limb0 = 0;
+        a.scratch = (u64*)c->take((size_t)(L - 1) * lane * 8);         // optional
+        e = wcrt_launch(a, st);
+    }
+    if (e == cudaSuccess) {
+        RescaleConsts k{};
+        for (int l = 0; l < L - 1; ++l) k.inv[l] = host::invmod(c->moduli[L - 1] % c->moduli[l], c->moduli[l]);
+        e = rescale_combine_launch((const u64*)in, (u64*)out, c->d_moduli, c->d_mu, cols, L, c->phi, k, st);
+    }
+    return done(e, "rescale_last");
 }
 
 // ---- GL permutation -----------------------------------------------------------------------------------------

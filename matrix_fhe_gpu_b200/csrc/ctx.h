@@ -39,6 +39,11 @@ struct mfhe_ctx {
     double2 *d_xyV = nullptr, *d_xyVT = nullptr, *d_xyVinv = nullptr, *d_xyVinvT = nullptr;   // [n][n]
     mfhe::u64 *d_crt_Q = nullptr, *d_crt_Qhalf = nullptr, *d_crt_M = nullptr, *d_crt_inv = nullptr;
     mfhe_ntt_plan* xy_plan = nullptr;
+    // sampler option (mfhe_ctx_set_sampler): 0 = the reference's index hashes (parity mode, default), 1 = Philox4x32-10
+    // keyed by `seed`; `draw` numbers the sampled arrays so that no two draws share randomness
+    int sampler_mode = 0;
+    uint64_t seed[2] = {0, 0};
+    uint64_t draw = 0;
     char* arena = nullptr;
     size_t arena_bytes = 0, arena_used = 0;
     // the arena is one scratch area shared by all calls on this context: calls are serialised on the host by arena_mu
@@ -156,6 +161,10 @@ struct RowArgs {                 // one launch over all phi*L*n rows of n coeffi
 struct SmallTables;
 cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulonglong2* mu, cudaStream_t st);
 cudaError_t sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi, cudaStream_t st);
+// sampler_sound.cu: kind 0 uniform [w][l][y][x], 1 gaussian (same), 2 ternary [w][l][x]
+cudaError_t sound_sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi,
+                                u64 seed0, u64 seed1, u64 draw, cudaStream_t st);
+void sound_cdt_copy(u64* h_out);            // the 83-entry cumulative table (tests)
 cudaError_t layout_launch(const u64* in, u64* out, int n, int limbs, int phi, int in_layout, int out_layout, cudaStream_t st);
 cudaError_t ct_add_launch(const u64* c1, const u64* c2, u64* res, const u64* moduli, size_t T, int n, int limbs,
                           int ref_index, cudaStream_t st);
@@ -165,6 +174,8 @@ cudaError_t trace_map_launch(const u64* Br, const u64* Bi, u64* Bpr, u64* Bpi, c
                              int batch, cudaStream_t st, int axis = 0);
 cudaError_t transpose_launch(const u64* in, u64* out, int n, size_t count, cudaStream_t st);
 struct RescaleConsts { u64 inv[64]; };
+cudaError_t rescale_combine_launch(const u64* in, u64* out, const u64* moduli, const ulonglong2* mu, int cols, int limbs, int phi,
+                                   const RescaleConsts& k, cudaStream_t st);
 cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                        const RescaleConsts& k, cudaStream_t st);
 bool trace_gemm_tc_eligible(int n, int limbs, const int* h_ndig);

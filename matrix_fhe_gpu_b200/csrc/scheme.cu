@@ -343,6 +343,25 @@ cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, cons
     return cudaGetLastError();
 }
 
+// RNS rescale by the last limb, final step: out[w][l][c] = (in[w][l][c] - out[w][l][c]) * q_last^-1 mod q_l, the input
+// having `limbs` limbs per lane and the output limbs - 1 (out holds the W-CRT of the centred last-limb coefficients)
+__global__ void rescale_combine_kernel(const u64* __restrict__ in, u64* __restrict__ out, const u64* __restrict__ moduli,
+                                       const ulonglong2* __restrict__ mu_tab, int cols, int limbs, size_t total,
+                                       const __grid_constant__ RescaleConsts k) {
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;       // over [w][limbs - 1][cols]
+    if (idx >= total) return;
+    const size_t c = idx % cols, wl = idx / cols, l = wl % (limbs - 1), w = wl / (limbs - 1);
+    const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
+    const u64 x = in[(w * limbs + l) * cols + c];
+    out[idx] = mul_barrett(sub_mod(x, out[idx], q), k.inv[l], q, mu.x, mu.y);
+}
+cudaError_t rescale_combine_launch(const u64* in, u64* out, const u64* moduli, const ulonglong2* mu, int cols, int limbs, int phi,
+                                   const RescaleConsts& k, cudaStream_t st) {
+    const size_t total = (size_t)phi * (limbs - 1) * cols;
+    rescale_combine_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, out, moduli, mu, cols, limbs, total, k);
+    return cudaGetLastError();
+}
+
 cudaError_t trace_rescale_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                  u64 inv0, u64 inv1, u64 inv2, cudaStream_t st) {
     const size_t total = (size_t)batch * limbs * n * n;

@@ -71,6 +71,11 @@ def _L():
         "mfhe_trace_map": [_vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_trace_gemm": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_trace_rescale": [_vp, _vp, _vp, _ci, _u64, _u64, _u64, _vp],
+        "mfhe_rescale_last": [_vp, _vp, _vp, _vp],
+        "mfhe_modup": [_vp, _vp, _vp, _vp, C.c_size_t, _vp],
+        "mfhe_moddown": [_vp, _vp, _vp, _vp, _vp, C.c_size_t, _vp],
+        "mfhe_ctx_set_sampler": [_vp, _ci, C.POINTER(_u64)],
+        "mfhe_sampler_cdt": [C.POINTER(_u64), _ci],
         "mfhe_trace_map_x": [_vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_trace_gemm_ty": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ci, _vp],
         "mfhe_transpose": [_vp, _vp, _vp, C.c_size_t, _vp],
@@ -288,6 +293,11 @@ class Context:
         check(_L().mfhe_decode_lane_from_rns_eval(self._h, _dev_ptr(re), _dev_ptr(im), _any_ptr(o), _stream_handle()))
         return o
 
+    def set_sampler(self, mode, seed=(0, 0)):
+        """mode 0: the reference's index hashes (parity); 1: Philox4x32-10 keyed by the 128-bit seed (mfhe_ctx_set_sampler)."""
+        arr = (_u64 * 2)(int(seed[0]), int(seed[1]))
+        check(_L().mfhe_ctx_set_sampler(self._h, int(mode), arr))
+
     # -- samplers / keys / encrypt / decrypt ----------------------------------------------------------------
     def sample_uniform(self):
         o = self._new(self.T); check(_L().mfhe_sample_uniform(self._h, _dev_ptr(o), _stream_handle())); return o
@@ -415,6 +425,12 @@ class Context:
         check(_L().mfhe_ct_matmul_decrypt(self._h, _dev_ptr(prod), _dev_ptr(sk), _dev_ptr(o[0]), _dev_ptr(o[1]), _stream_handle()))
         return o
 
+    def rescale_last(self, x):
+        """mfhe_rescale_last: [w][L][n^2] -> [w][L-1][n^2], divided by the last modulus."""
+        o = self._new(self.phi * (self.L - 1) * self.n2, like=x)
+        check(_L().mfhe_rescale_last(self._h, _dev_ptr(x), _dev_ptr(o), _stream_handle()))
+        return o
+
     def conj_lane(self):
         """l -> l' with exp[l'] = -exp[l] mod p (see encrypted_matmul)."""
         import numpy as np
@@ -437,6 +453,31 @@ class Context:
         pr, pi = self.ct_matmul_decrypt(prod, sk)
         out = self.decode_eval_pair(pr, pi, MATRIX)            # divides by delta once; the product carries delta^2
         return (out / self.delta).reshape(self.phi, self.n, self.n)
+
+
+def modup(plan_qp, q_to_p, x, batch):
+    """mfhe_modup: x [batch][LQ][N] coefficient form -> [batch][LQ+LP][N] NTT form (plan_qp: NttPlan over Q then P)."""
+    import torch
+    o = torch.empty(batch * plan_qp.limbs * plan_qp.n, dtype=torch.int64, device=x.device)
+    check(_L().mfhe_modup(plan_qp._h, q_to_p._h, _dev_ptr(x), _dev_ptr(o), batch, _stream_handle()))
+    return o
+
+
+def moddown(plan_qp, p_to_q, x, batch):
+    """mfhe_moddown: x [batch][LQ+LP][N] NTT form -> [batch][LQ][N] NTT form, divided by P."""
+    import torch
+    lq, lp = len(p_to_q.p), len(p_to_q.q)
+    o = torch.empty(batch * lq * plan_qp.n, dtype=torch.int64, device=x.device)
+    scratch = torch.empty(batch * lp * plan_qp.n, dtype=torch.int64, device=x.device)
+    check(_L().mfhe_moddown(plan_qp._h, p_to_q._h, _dev_ptr(x), _dev_ptr(o), _dev_ptr(scratch), batch, _stream_handle()))
+    return o
+
+
+def sampler_cdt():
+    import numpy as np
+    arr = (_u64 * 83)()
+    check(_L().mfhe_sampler_cdt(arr, 83))
+    return np.asarray(list(arr), dtype=np.uint64)
 
 
 def gl_perm_tables(n):

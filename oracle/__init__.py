@@ -74,6 +74,10 @@ def lib() -> C.CDLL:
                                                    _p64, _p64, _p64, _p64, _p64]
         L.mfo_num_threads.restype = C.c_int
         L.mfo_set_num_threads.restype = None; L.mfo_set_num_threads.argtypes = [C.c_int]
+        L.mfo_philox4x32_10.restype = None; L.mfo_philox4x32_10.argtypes = [_p32, C.c_uint32, C.c_uint32]
+        L.mfo_sound_cdt.restype = None; L.mfo_sound_cdt.argtypes = [_p64]
+        L.mfo_sound_sample.restype = None
+        L.mfo_sound_sample.argtypes = [C.c_int, _p64, _p64, C.c_int, C.c_int, C.c_int, u64, u64, u64]
         L.mfo_gl_get_psi.restype = u64; L.mfo_gl_get_psi.argtypes = [u64, C.c_int]
         for name in ("mfo_gl_forward", "mfo_gl_backward", "mfo_cyclic_forward", "mfo_cyclic_backward"):
             getattr(L, name).restype = None
@@ -113,6 +117,24 @@ def use_all_cores() -> int:
         n = os.cpu_count() or 1
     lib().mfo_set_num_threads(n)
     return lib().mfo_num_threads()
+
+
+def philox4x32_10(ctr, key):
+    c = np.asarray(ctr, dtype=np.uint32).copy()
+    lib().mfo_philox4x32_10(c, int(key[0]), int(key[1]))
+    return [int(v) for v in c]
+
+
+def sound_cdt():
+    t = np.zeros(83, dtype=np.uint64); lib().mfo_sound_cdt(t); return t
+
+
+def sound_sample(kind, moduli, n, phi, seed, draw):
+    """kind 0 uniform / 1 gaussian: [phi][L][n][n]; 2 ternary: [phi][L][n]  (sampler_oracle.c)."""
+    mods = np.ascontiguousarray(np.asarray(moduli, dtype=np.uint64))
+    out = np.zeros(phi * len(mods) * (n if kind == 2 else n * n), dtype=np.uint64)
+    lib().mfo_sound_sample(kind, out, mods, n, len(mods), phi, int(seed[0]), int(seed[1]), int(draw))
+    return out
 
 
 def get_primes(ntt_size: int, bits: int, count: int) -> np.ndarray:
@@ -250,6 +272,7 @@ def _scheme_lib():
         "mfo_trace_map": [vp, _p64, _p64, _p64, _p64, ci],
         "mfo_trace_gemm": [vp, _p64, _p64, _p64, _p64, _p64, _p64, ci],
         "mfo_trace_rescale": [vp, _p64, _p64, ci, u64, u64, u64],
+        "mfo_rescale_last": [vp, _p64, _p64],
         "mfo_trace_map_x": [vp, _p64, _p64, _p64, _p64, ci],
         "mfo_trace_gemm_ty": [vp, _p64, _p64, _p64, _p64, _p64, _p64, ci],
         "mfo_ct_matmul": [vp, _p64, _p64, _p64, _p64, _p64],
@@ -482,6 +505,9 @@ class SchemeCtx:
 
     def ct_matmul_decrypt(self, prod, sk):
         o = [self._u(self.T), self._u(self.T)]; self._L.mfo_ct_matmul_decrypt(self._h, prod, sk, o[0], o[1]); return o
+
+    def rescale_last(self, x):
+        o = self._u(self.phi * (self.L - 1) * self.n2); self._L.mfo_rescale_last(self._h, self._c(x, np.uint64).reshape(-1), o); return o
 
     def conj_lane(self):
         """Involution l -> l' of the W lanes with exp[l'] = -exp[l] mod p: coefficient-wise conjugation of an encoded

@@ -80,6 +80,11 @@ void mfo_negacyclic_inverse_batch(uint64_t *data, size_t batch, size_t L, int lo
                                   const uint64_t *n_inv, const uint64_t *n_inv_shoup);
 int mfo_num_threads(void);
 void mfo_set_num_threads(int n);
+/* sampler_oracle.c: the sound sampler option */
+void mfo_philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1);
+void mfo_sound_cdt(uint64_t *out83);
+void mfo_sound_sample(int kind, uint64_t *out, const uint64_t *moduli, int n, int limbs, int phi, uint64_t seed0, uint64_t seed1,
+                      uint64_t draw);
 
 /* ---- reference "gl" convention, ring Z_q[X]/(X^n - i) ------------------- */
 /* src/core/ntt_core.cu:49-70 get_psi: smallest base >= 2 giving order 4n.   */

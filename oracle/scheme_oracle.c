@@ -480,6 +480,36 @@ void mfo_ct_matmul_decrypt(const mfo_ctx *c, const uint64_t *prod, const uint64_
     free(acc); free(e); free(at); free(et);
 }
 
+/* ---- RNS rescale of the matrix scheme: X' = (X - [X]_{q_last}) / q_last on the W-coefficients,
+ * stated per column with the definitions of the W-CRT (HE.cu:716-781): in [w][L][n^2] -> out [w][L-1][n^2] ---------- */
+void mfo_rescale_last(const mfo_ctx *c, const uint64_t *in, uint64_t *out) {
+    const size_t phi = (size_t)c->phi, L = (size_t)c->L, cols = (size_t)c->n * c->n;
+    const uint64_t ql = c->moduli[L - 1];
+    const uint64_t *Vi = c->wntt_inv + (L - 1) * phi * phi;          /* [w][r] = V^-1[r][w] */
+#pragma omp parallel for schedule(static)
+    for (long col = 0; col < (long)cols; ++col) {
+        int64_t cen[1024];
+        for (size_t r = 0; r < phi; ++r) {
+            uint64_t acc = 0;
+            for (size_t w = 0; w < phi; ++w)
+                acc = mfo_addmod(acc, mfo_mulmod(in[(w * L + (L - 1)) * cols + (size_t)col], Vi[w * phi + r], ql), ql);
+            cen[r] = acc > (ql >> 1) ? (int64_t)acc - (int64_t)ql : (int64_t)acc;
+        }
+        for (size_t l = 0; l + 1 < L; ++l) {
+            const uint64_t q = c->moduli[l], qinv = mfo_invmod(ql % q, q);
+            const uint64_t *V = c->wntt + l * phi * phi;             /* [w][r] */
+            for (size_t w = 0; w < phi; ++w) {
+                uint64_t acc = 0;
+                for (size_t r = 0; r < phi; ++r) {
+                    int64_t m = cen[r] % (int64_t)q; if (m < 0) m += (int64_t)q;
+                    acc = mfo_addmod(acc, mfo_mulmod((uint64_t)m, V[w * phi + r], q), q);
+                }
+                out[(w * (L - 1) + l) * cols + (size_t)col] = mfo_mulmod(mfo_submod(in[(w * L + l) * cols + (size_t)col], acc, q), qinv, q);
+            }
+        }
+    }
+}
+
 /* ---- Phantom bConv_BEHZ: ph/src/rns_bconv.cu:22-29, 109-131, 212-229 ------------------------------ */
 void mfo_bconv(const uint64_t *in, uint64_t *out, size_t N, int L_in, const uint64_t *q_in, int L_out, const uint64_t *p_out) {
     uint64_t *qhat_inv = (uint64_t *)malloc((size_t)L_in * 8), *qhat_mod_p = (uint64_t *)malloc((size_t)L_in * L_out * 8);

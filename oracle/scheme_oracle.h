@@ -137,6 +137,7 @@ void mfo_trace_map(const mfo_ctx *c, const uint64_t *Br, const uint64_t *Bi, uin
 void mfo_trace_gemm(const mfo_ctx *c, const uint64_t *Ar, const uint64_t *Ai, const uint64_t *Bpr, const uint64_t *Bpi,
                     uint64_t *Cr, uint64_t *Ci, int batch);
 void mfo_trace_rescale(const mfo_ctx *c, uint64_t *Cr, uint64_t *Ci, int batch, uint64_t inv0, uint64_t inv1, uint64_t inv2);
+void mfo_rescale_last(const mfo_ctx *c, const uint64_t *in, uint64_t *out);
 /* encrypted matrix product */
 void mfo_trace_map_x(const mfo_ctx *c, const uint64_t *Br, const uint64_t *Bi, uint64_t *Bpr, uint64_t *Bpi, int batch);
 void mfo_trace_gemm_ty(const mfo_ctx *c, const uint64_t *Ur, const uint64_t *Ui, const uint64_t *Vr, const uint64_t *Vi,

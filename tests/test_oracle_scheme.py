@@ -298,3 +298,42 @@ def test_encrypted_matmul_decrypts_to_the_plaintext_product():
     tr = lambda a: np.ascontiguousarray(a.reshape(o.phi, o.L, o.n, o.n).transpose(0, 1, 3, 2)).reshape(-1)
     plain = o.decode_eval_pair(o.matrix_to_poly(tr(dr)), o.matrix_to_poly(tr(di))).reshape(o.phi, o.n, o.n) / o.delta
     assert np.abs(plain - want).max() <= 2.0 ** -24 * np.abs(want).max()
+
+
+# ---- RNS rescale of the matrix scheme ----
+def test_rescale_last_is_exact_division_on_the_w_coefficients():
+    """X' = (X - [X]_{q_last}) / q_last for every integer W-coefficient, checked with Python integers through the
+    CRT of the remaining limbs; X spans the whole range (-Q/2, Q/2)."""
+    mods = O.primes_congruent_one(960, 45, 1) + O.primes_congruent_one(960, 35, 3)
+    o = O.SchemeCtx(16, 5, mods, 2.0 ** 30)
+    o1 = O.SchemeCtx(16, 5, mods[:-1], 2.0 ** 30)
+    Q = 1
+    for q in mods:
+        Q *= q
+    ql, Q1 = mods[-1], Q // mods[-1]
+    rng = np.random.default_rng(9)
+    X = [int(rng.integers(0, 2 ** 62)) * int(rng.integers(0, 2 ** 62)) * int(rng.integers(0, 2 ** 40)) % Q - Q // 2
+         for _ in range(o.phi * o.n2)]
+    X[0], X[1], X[2] = 0, ql, -ql // 2                             # edge cases
+    coeff = np.zeros((o.phi, o.L, o.n2), dtype=np.uint64)         # W-coeff, matrix-major [r][l][pos]
+    for r in range(o.phi):
+        for pos in range(o.n2):
+            for l, q in enumerate(mods):
+                coeff[r, l, pos] = X[r * o.n2 + pos] % q
+    ev = o.poly_to_matrix(o.wntt_forward_matrix(coeff.reshape(-1)))
+    out = o.rescale_last(ev)
+    back = o1.wntt_inverse_matrix(o1.matrix_to_poly(out)).reshape(o.phi, o.L - 1, o.n2)
+    for r in range(0, o.phi):
+        for pos in range(0, o.n2, 7):
+            x = X[r * o.n2 + pos]
+            c = x % ql
+            c = c - ql if c > ql // 2 else c
+            want = (x - c) // ql
+            assert (x - c) % ql == 0
+            got = 0
+            for l, q in enumerate(mods[:-1]):
+                M = Q1 // q
+                got += M * (int(back[r, l, pos]) * pow(M % q, -1, q) % q)
+            got %= Q1
+            got = got - Q1 if got > Q1 // 2 else got
+            assert got == want
