@@ -85,7 +85,9 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
 
     for L, tag in ((11, "config3_encode_decode_L11"), (24, "config4_pipeline_L24")):
         mods = (S.REF_MODULI + L24_EXTRA)[:L]
+        torch.cuda.synchronize(); t_ctx = time.perf_counter()
         g = S.Context(moduli=mods)
+        torch.cuda.synchronize(); t_ctx = (time.perf_counter() - t_ctx) * 1e3
         ell, i = np.meshgrid(np.arange(g.phi, dtype=np.float64), np.arange(g.n2, dtype=np.float64), indexing="ij")
         m = torch.from_numpy((ell + 0.001 * i) * (1 - 1j)).reshape(-1).to(dev)
         sk = g.generate_secret_key()
@@ -137,7 +139,10 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
                 g.decrypt_and_decode(ct_r, ct_i, zero, dec)
             out[tag] = {"ms_per_batch": timed(loop, 3), "encode_ms": timed(lambda: g.encode_to_wntt_eval(m), 3),
                         "decrypt_decode_ms": timed(lambda: g.decrypt_and_decode(ct_r, ct_i, zero, dec), 3),
-                        "batch": "512 lanes x 64x64 complex fp64 (2^21 values)", "max_err": err}
+                        "batch": "512 lanes x 64x64 complex fp64 (2^21 values)", "max_err": err,
+                        "context_create_ms": t_ctx,
+                        "context_create_note": "mfhe_ctx_create: W-CRT tables built on the device (wtables_gpu.cu); the "
+                                               "reference's init_he_backend is baselines.reference_cuda.init_he_backend_ms"}
             S_bytes = g.T * 8
             fl = pipeline_floors(g, mods, 4, 6 * S_bytes + 2 * g.phi * g.n2 * 16)     # encode: 32 MiB + 2S, decode: 4S + 32 MiB
             msb = out[tag]["ms_per_batch"]
@@ -166,7 +171,7 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
             assert errf < 1e-3, errf
             out[tag] = {"pairs_per_s": world * pairs_per_rank / (ms * 1e-3), "ciphertexts_per_s": 2 * world * pairs_per_rank / (ms * 1e-3),
                         "ms_per_pair": ms / pairs_per_rank, "ms_per_pair_three_calls": ms3 / pairs_per_rank,
-                        "pairs_per_rank_per_step": pairs_per_rank, "max_err": max(err, errf),
+                        "pairs_per_rank_per_step": pairs_per_rank, "max_err": max(err, errf), "context_create_ms": t_ctx,
                         "note": "mfhe_encode_encrypt_pair -> decrypt_and_decode (three_calls: encode -> encrypt_pair -> "
                                 "decrypt_and_decode, identical ciphertexts), one (re, im) pair = 2 ciphertexts of 768 MiB"}
             S_bytes = g.T * 8

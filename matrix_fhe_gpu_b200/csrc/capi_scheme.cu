@@ -84,12 +84,17 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
     while ((1 << c->logn) < n) ++c->logn;
     c->moduli.assign(p->moduli, p->moduli + L);
     const size_t phi = (size_t)c->phi, pp = phi * phi;
-    std::vector<uint64_t> tab_fwd((size_t)L * pp), tab_inv((size_t)L * pp);
+    // W-CRT tables: built on the device (wtables_gpu.cu) unless MFHE_TABLES_HOST is set (the host closed form below,
+    // kept as the cross-check path: tests compare the two word for word)
+    const bool host_tables = std::getenv("MFHE_TABLES_HOST") != nullptr;
+    std::vector<uint64_t> tab_fwd(host_tables ? (size_t)L * pp : 0), tab_inv(tab_fwd.size());
     std::vector<host::TwPair> mu(L);
     const bool want_digits = (phi % 64 == 0);               // the tensor-core W-CRT tiling (wcrt_tc.cu)
-    std::vector<unsigned char> dig_fwd(want_digits ? (size_t)L * 8 * pp : 0), dig_inv(dig_fwd.size());
+    std::vector<unsigned char> dig_fwd(want_digits && host_tables ? (size_t)L * 8 * pp : 0), dig_inv(dig_fwd.size());
     const bool want_tiles = (phi % 128 == 0);                // tcgen05 tiling (wcrt_umma.cu)
-    std::vector<unsigned char> digt_fwd(want_tiles ? (size_t)L * 8 * pp : 0), digt_inv(digt_fwd.size());
+    std::vector<unsigned char> digt_fwd(want_tiles && host_tables ? (size_t)L * 8 * pp : 0), digt_inv(digt_fwd.size());
+    std::vector<uint64_t> h_ieta(L), h_pinv(L);
+    std::vector<int> Phi;
     c->ndig.assign(L, 8);
     std::vector<host::cplx> wV, wVinv, xV, xVinv;
     host::CrtTables crt;
@@ -106,17 +111,19 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
         }
         c->wsplit = small ? 1 : 0;
         c->wexp = host::unit_exponents(f);
-        const std::vector<int> Phi = host::cyclotomic_3f(f);
-        c->hV.resize((size_t)L * pp); c->hVinv.resize((size_t)L * pp);
+        Phi = host::cyclotomic_3f(f);
         for (int l = 0; l < L; ++l) {
             const uint64_t q = c->moduli[l];
             const uint64_t eta = host::find_eta(q, f);
             if (!eta) throw std::runtime_error("no element of order p mod " + std::to_string(q));
             c->eta.push_back(eta);
+            h_ieta[l] = host::invmod(eta, q); h_pinv[l] = host::invmod((uint64_t)c->p % q, q);
+            { int bits = 0; while (bits < 64 && (q >> bits)) ++bits; c->ndig[l] = (bits + 7) / 8; }
+            const unsigned __int128 m128 = ~(unsigned __int128)0 / q;
+            mu[l] = host::TwPair{(uint64_t)m128, (uint64_t)(m128 >> 64)};
+            if (!host_tables) continue;
             std::vector<uint64_t> V, Vinv;
             host::build_wcrt_limb(q, f, c->wexp, Phi, eta, V, Vinv);
-            std::memcpy(&c->hV[(size_t)l * pp], V.data(), pp * 8);
-            std::memcpy(&c->hVinv[(size_t)l * pp], Vinv.data(), pp * 8);
             // GEMM tables [i][o]: forward i = r (W-coeff), o = w  -> V[w][r];  inverse i = w, o = r -> Vinv[r][w]
             auto pack = [&](uint64_t v) { return small ? ((v & ((1ull << 26) - 1)) | ((v >> 26) << 32)) : v; };
             for (size_t i = 0; i < phi; ++i)
@@ -124,7 +131,6 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
                     tab_fwd[(size_t)l * pp + i * phi + o] = pack(V[o * phi + i]);
                     tab_inv[(size_t)l * pp + i * phi + o] = pack(Vinv[o * phi + i]);
                 }
-            { int bits = 0; while (bits < 64 && (q >> bits)) ++bits; c->ndig[l] = (bits + 7) / 8; }
             if (want_digits)
                 for (int u = 0; u < 8; ++u)
                     for (size_t k = 0; k < pp; ++k) {
@@ -143,8 +149,6 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
                         }
                     }
             }
-            const unsigned __int128 m = ~(unsigned __int128)0 / q;
-            mu[l] = host::TwPair{(uint64_t)m, (uint64_t)(m >> 64)};
         }
         host::build_wdft(f, c->wexp, Phi, wV, wVinv);
         host::build_xy(n, xV, xVinv);
@@ -198,11 +202,21 @@ extern "C" int mfhe_ctx_create(const mfhe_params* p, mfhe_ctx** out) {
 
     cudaError_t e = cudaSuccess;
 #define UP(dst, vec) if (e == cudaSuccess) e = upload(dst, (vec).data(), (vec).size() * sizeof((vec)[0]))
-    UP(c->d_moduli, c->moduli); UP(c->d_mu, mu); UP(c->d_wtab_fwd, tab_fwd); UP(c->d_wtab_inv, tab_inv);
+    UP(c->d_moduli, c->moduli); UP(c->d_mu, mu);
+    if (host_tables) {
+        UP(c->d_wtab_fwd, tab_fwd); UP(c->d_wtab_inv, tab_inv);
+        if (want_digits) { UP(c->d_wdig_fwd, dig_fwd); UP(c->d_wdig_inv, dig_inv); }
+        if (want_tiles) { UP(c->d_wdigt_fwd, digt_fwd); UP(c->d_wdigt_inv, digt_inv); }
+    } else {
+#define AL(dst, bytes) if (e == cudaSuccess) e = cudaMalloc((void**)&(dst), (bytes))
+        AL(c->d_wtab_fwd, (size_t)L * pp * 8); AL(c->d_wtab_inv, (size_t)L * pp * 8);
+        if (want_digits) { AL(c->d_wdig_fwd, (size_t)L * 8 * pp); AL(c->d_wdig_inv, (size_t)L * 8 * pp); }
+        if (want_tiles) { AL(c->d_wdigt_fwd, (size_t)L * 8 * pp); AL(c->d_wdigt_inv, (size_t)L * 8 * pp); }
+#undef AL
+        if (e == cudaSuccess) e = wtables_build_device(c, (const u64*)c->eta.data(), (const u64*)h_ieta.data(), (const u64*)h_pinv.data(), Phi.data(), nullptr);
+    }
     UP(c->d_wdft_fwd, wf); UP(c->d_wdft_inv, wi);
     if (hp) { UP(c->d_wpairs, wpairs); UP(c->d_wdfth_fwd, whf); UP(c->d_wdfth_inv, whi); }
-    if (want_digits) { UP(c->d_wdig_fwd, dig_fwd); UP(c->d_wdig_inv, dig_inv); }
-    if (want_tiles) { UP(c->d_wdigt_fwd, digt_fwd); UP(c->d_wdigt_inv, digt_inv); }
     UP(c->d_xyV, xV); UP(c->d_xyVT, xVT); UP(c->d_xyVinv, xVinv); UP(c->d_xyVinvT, xVinvT);
     UP(c->d_crt_Q, crt.Q); UP(c->d_crt_Qhalf, crt.Qhalf); UP(c->d_crt_M, crt.M); UP(c->d_crt_inv, crt.inv);
 #undef UP
@@ -235,9 +249,18 @@ extern "C" uint64_t mfhe_ctx_eta(const mfhe_ctx* c, int l) { return (c && l >= 0
 extern "C" int mfhe_ctx_get_wcrt_table(const mfhe_ctx* c, int l, int inverse, uint64_t* h) {
     if (!c || !h || l < 0 || l >= c->L) return fail(MFHE_EINVAL, "get_wcrt_table: bad argument");
     const size_t phi = (size_t)c->phi, pp = phi * phi;
-    if (!inverse) { std::memcpy(h, &c->hV[(size_t)l * pp], pp * 8); return MFHE_OK; }
-    for (size_t w = 0; w < phi; ++w)                       // reference layout: [w][r] = Vinv[r][w]
-        for (size_t r = 0; r < phi; ++r) h[w * phi + r] = c->hVinv[(size_t)l * pp + r * phi + w];
+    // read back from the device GEMM table [i][o] (split-26 packing undone): forward i = r, o = w -> V[w][r];
+    // inverse i = w, o = r -> the reference's inv_table[l][w][r] = V^-1[r][w] (HE.cu:263-266)
+    std::vector<uint64_t> t(pp);
+    cudaError_t e = cudaMemcpy(t.data(), (inverse ? c->d_wtab_inv : c->d_wtab_fwd) + (size_t)l * pp, pp * 8, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return cuda_fail(e, "get_wcrt_table");
+    auto unpack = [&](uint64_t v) { return c->wsplit ? ((v & 0xffffffffull) | ((v >> 32) << 26)) : v; };
+    if (!inverse) {
+        for (size_t w = 0; w < phi; ++w)
+            for (size_t r = 0; r < phi; ++r) h[w * phi + r] = unpack(t[r * phi + w]);
+        return MFHE_OK;
+    }
+    for (size_t i = 0; i < pp; ++i) h[i] = unpack(t[i]);
     return MFHE_OK;
 }
 extern "C" int mfhe_ctx_get_crt(const mfhe_ctx* c, int which, uint64_t* h) {

@@ -15,7 +15,6 @@ struct mfhe_ctx {
     double delta = 0;
     std::vector<uint64_t> moduli, eta;
     std::vector<uint16_t> wexp;
-    std::vector<uint64_t> hV, hVinv;          // [L][phi][phi]: V[w][r] and V^-1[r][w] (row-major)
     std::vector<uint64_t> hQ, hQhalf, hM, hInv;
     // device tables
     mfhe::u64* d_moduli = nullptr;            // [L]
@@ -82,6 +81,9 @@ struct ArenaScope {
 };
 
 namespace mfhe {
+// wtables_gpu.cu: V_l, V_l^-1 in all device layouts, built on the device (closed form); buffers must be allocated
+cudaError_t wtables_build_device(mfhe_ctx* c, const u64* h_eta, const u64* h_ieta, const u64* h_pinv, const int* h_Phi,
+                                 cudaStream_t st);
 
 // ---- W-CRT as a per-limb modular GEMM  out[o][col] = sum_i tab[limb][i][o] * in[i][col] ----------
 enum WcrtSource { kSrcMem = 0, kSrcI64 = 1, kSrcQuantRe = 2, kSrcQuantIm = 3, kSrcUniform = 4, kSrcGauss = 5 };

@@ -192,3 +192,22 @@ def test_native_wcrt_three_paths_identical(G, cuda_device, monkeypatch):
             for k, (x, y) in enumerate(zip(ref, got)):
                 assert torch.equal(x, y), f"path {path} differs from cuda-core at output {k}"
     monkeypatch.delenv("MFHE_WCRT_PATH")
+
+
+def test_device_built_tables_equal_host_closed_form(G, cuda_device, monkeypatch):
+    """SURVEY 8(f) rank 3: the W-CRT tables come from wtables_gpu.cu (one CTA per (limb, lane), closed-form inverse);
+    MFHE_TABLES_HOST=1 selects the host closed form.  Every table word of every limb and the transforms through all
+    four device layouts (GEMM tables, digit planes, UMMA tiles) must agree, and both equal the oracle (test_native_tables)."""
+    import torch
+    S, g = G
+    monkeypatch.setenv("MFHE_TABLES_HOST", "1")
+    h = S.Context()
+    monkeypatch.delenv("MFHE_TABLES_HOST")
+    for l in range(g.L):
+        assert (g.wcrt_table(l) == h.wcrt_table(l)).all() and (g.wcrt_table(l, True) == h.wcrt_table(l, True)).all()
+    a = g.sample_uniform()
+    for path in ("cuda", "mma", "umma"):
+        monkeypatch.setenv("MFHE_WCRT_PATH", path)
+        assert torch.equal(g.wntt_forward_matrix(a), h.wntt_forward_matrix(a))
+        assert torch.equal(g.wntt_inverse_matrix(a, S.MATRIX, S.MATRIX), h.wntt_inverse_matrix(a, S.MATRIX, S.MATRIX))
+    monkeypatch.delenv("MFHE_WCRT_PATH")
