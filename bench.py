@@ -282,20 +282,26 @@ def config5_block(dev, world, rank, dist, steps=10):
     x_loc = O.splitmix64(idx) % np.asarray(q[qs:qs + qc], dtype=np.uint64).reshape(1, -1, 1)
     x0 = torch.from_numpy(x_loc.view(np.int64)).to(dev)
     work = torch.empty_like(x0)
-    kind, groups = "none (one GPU, unsharded)", 1
+    kind, groups, ipc, symm_ok = "none (one GPU, unsharded)", 1, None, False
     if world > 1:
         try:
-            sh.enable_p2p(batch)
-            kind, groups = "fused: bconv kernel stores partial sums into the owners' symmetric-memory buffers over NVLink, one device barrier", 2
+            ipc = SH.IpcComm(rank, world, lout, n, batch)
+            kind = ("mfhe_bconv_sharded_step (C ABI): bconv kernel stores partial sums into the owners' CUDA-IPC receive "
+                    "buffers over NVLink, flag barrier (release/acquire.sys), no NCCL")
         except Exception as e:                              # noqa: BLE001
-            kind = f"NCCL all_to_all of partial sums (symmetric memory unavailable: {e!r})"[:200]
+            kind = f"NCCL all_to_all of partial sums (CUDA IPC unavailable: {e!r})"[:200]
+        try:
+            sh.enable_p2p(batch)
+            symm_ok = True
+        except Exception:                                   # noqa: BLE001
+            symm_ok = False
 
     def step():
         work.copy_(x0)
         if world == 1:
             return sh.step_unsharded(work, batch)
-        if kind.startswith("fused"):
-            return sh.step_p2p(work, batch, groups)
+        if ipc is not None:
+            return ipc.step(sh, work, batch)
         return sh.step(work, batch)
 
     out = None
@@ -322,7 +328,7 @@ def config5_block(dev, world, rank, dist, steps=10):
     stages = None
     if world > 1:
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        if kind.startswith("fused"):
+        if symm_ok:
             acc = np.zeros(4)
             for _ in range(5):
                 work.copy_(x0)
@@ -339,6 +345,20 @@ def config5_block(dev, world, rank, dist, steps=10):
            "parity": "ok" if bool(flag.item()) else "FAILED",
            "parity_check": "poly 0, every rank's output limbs, vs the CPU oracle (INTT + bConv_BEHZ + NTT restated)",
            "algorithmic_bytes_per_step": batch * n * 8 * (2 * lin + 2 * lout)}
+    if world > 1 and symm_ok:                               # the torch symmetric-memory form of the same exchange, two stream groups
+        def step2():
+            work.copy_(x0)
+            return sh.step_p2p(work, batch, 2)
+        for _ in range(3):
+            step2()
+        torch.cuda.synchronize(); dist.barrier()
+        ev[0].record()
+        for _ in range(steps):
+            step2()
+        ev[1].record(); torch.cuda.synchronize()
+        t2 = torch.tensor([ev[0].elapsed_time(ev[1]) / steps], device=dev)
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        blk["alt_symmetric_memory_two_streams_ms_per_step"] = float(t2.item())
     if stages:
         blk["stage_ms"] = {"intt": stages[0], "scatter": stages[1], "barrier": stages[2], "reduce_ntt": stages[3],
                            "note": "one stream group, CUDA events between the stages, max over ranks"}

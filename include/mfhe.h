@@ -291,6 +291,25 @@ int mfhe_ct_matmul(mfhe_ctx *ctx, const uint64_t *d_ctU_re, const uint64_t *d_ct
 /* decrypts the 4-component product (d_prod is consumed as scratch); out = evals [w][l][z][x] of n * sum_y U V' */
 int mfhe_ct_matmul_decrypt(mfhe_ctx *ctx, uint64_t *d_prod, const uint64_t *d_sk, uint64_t *d_out_re, uint64_t *d_out_im, void *stream);
 
+/* ---- multi-GPU: limb-sharded base conversion (BASELINE config 5).  One process per GPU.  The exchange
+ * is fused into the base-conversion kernel (its stores go to peer memory over NVLink); the communicator only holds the
+ * double-buffered receive buffers and barrier flags, shared between the processes as CUDA IPC handles that the HOST program
+ * moves (MFHE_COMM_HANDLE_BYTES per rank, any transport).  No NCCL, no collective. ---- */
+typedef struct mfhe_comm mfhe_comm;
+#define MFHE_COMM_HANDLE_BYTES 192
+size_t mfhe_bconv_sharded_recv_words(int world, int l_out, size_t N, size_t batch);     /* receive-buffer size for create */
+int mfhe_comm_create(int rank, int world, size_t recv_words, mfhe_comm **out);
+void mfhe_comm_destroy(mfhe_comm *comm);
+int mfhe_comm_export(const mfhe_comm *comm, void *h_handle /* MFHE_COMM_HANDLE_BYTES */);
+int mfhe_comm_import(mfhe_comm *comm, const void *h_all_handles /* world x MFHE_COMM_HANDLE_BYTES, rank order */);
+int mfhe_comm_barrier(mfhe_comm *comm, void *stream);            /* stream-ordered, release / acquire at system scope */
+/* INTT(own Q-limbs) -> partial sums stored into the owners' receive buffers -> barrier -> reduce -> NTT(own P-limbs).
+ * plan_q / plan_p / bconv cover the FULL bases; d_x_local [batch][q_count][N] (destroyed), d_out [batch][p_count][N];
+ * rank r owns the r-th balanced contiguous window of each base (Phantom: nwt_2d_radix8_backward_inplace + bConv_BEHZ +
+ * nwt_2d_radix8_forward_inplace on one GPU, ph/src/rns_bconv.cu:212-229). */
+int mfhe_bconv_sharded_step(mfhe_comm *comm, const mfhe_ntt_plan *plan_q, const mfhe_ntt_plan *plan_p,
+                            const mfhe_bconv_plan *bconv, uint64_t *d_x_local, uint64_t *d_out, size_t batch, void *stream);
+
 /* ---- mod-up / mod-down with an auxiliary base P (config.h:22,46-52 reserves P_MODULI, Phantom:
  * ph/src/ntt/ntt_modup.cu, ntt_moddown.cu, ph/src/rns_bconv.cu:530-830).  `qp` is a flat plan whose limbs are Q then P.
  * mod-up:   d_x [batch][LQ][N] COEFFICIENT form over Q -> d_out [batch][LQ+LP][N] NTT form over Q u P (q_to_p: Q -> P).

@@ -104,6 +104,61 @@ def emulate_exchange(partials, out_windows: Sequence[Tuple[int, int]], rank: int
     return torch.stack([p[:, s:s + c, :] for p in partials]).contiguous()
 
 
+class IpcComm:
+    """mfhe_comm (csrc/comm.cu): the C-ABI form of the fused exchange -- receive buffers and barrier flags shared between
+    the processes as CUDA IPC handles, no NCCL and no torch symmetric memory in the data path.  torch.distributed is used
+    ONCE, to move the 192-byte handles (a C++ host would use its own transport)."""
+
+    def __init__(self, rank: int, world: int, l_out: int, n: int, batch: int, group=None):
+        import ctypes as C
+        from . import lib, check
+        L = lib()
+        L.mfhe_bconv_sharded_recv_words.restype = C.c_size_t
+        L.mfhe_bconv_sharded_recv_words.argtypes = [C.c_int, C.c_int, C.c_size_t, C.c_size_t]
+        L.mfhe_comm_create.argtypes = [C.c_int, C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.mfhe_comm_destroy.argtypes = [C.c_void_p]; L.mfhe_comm_destroy.restype = None
+        L.mfhe_comm_export.argtypes = [C.c_void_p, C.c_void_p]
+        L.mfhe_comm_import.argtypes = [C.c_void_p, C.c_void_p]
+        L.mfhe_comm_barrier.argtypes = [C.c_void_p, C.c_void_p]
+        L.mfhe_bconv_sharded_step.argtypes = [C.c_void_p] * 6 + [C.c_size_t, C.c_void_p]
+        self._L, self.rank, self.world = L, rank, world
+        words = L.mfhe_bconv_sharded_recv_words(world, l_out, n, batch)
+        h = C.c_void_p()
+        check(L.mfhe_comm_create(rank, world, words, C.byref(h)))
+        self._h = h
+        if world > 1:
+            import torch.distributed as dist
+            mine = C.create_string_buffer(192)
+            check(L.mfhe_comm_export(h, mine))
+            gathered = [None] * world
+            dist.all_gather_object(gathered, bytes(mine.raw), group=group)
+            allh = C.create_string_buffer(b"".join(gathered), 192 * world)
+            check(L.mfhe_comm_import(h, allh))
+            dist.barrier(group=group)                     # every rank has opened every peer before the first store
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                self._L.mfhe_comm_destroy(h)
+            except Exception:
+                pass
+
+    def barrier(self):
+        from . import check, _stream_handle
+        check(self._L.mfhe_comm_barrier(self._h, _stream_handle()))
+
+    def step(self, sh: "LimbShardedBconv", x_local, batch: int):
+        """mfhe_bconv_sharded_step: the whole config-5 step of this rank in one C call."""
+        import torch
+        from . import check, _dev_ptr, _stream_handle
+        pc = sh.p_windows[self.rank][1]
+        out = torch.empty(batch * pc * sh.n, dtype=torch.int64, device=x_local.device)
+        check(self._L.mfhe_bconv_sharded_step(self._h, sh.plan_q._h, sh.plan_p._h, sh.bconv._h, _dev_ptr(x_local), _dev_ptr(out),
+                                              batch, _stream_handle()))
+        return out.view(batch, pc, sh.n)
+
+
 class LimbShardedBconv:
     """Config 5 step on one rank: INTT(own Q-limbs) -> partial base conversion -> exchange -> reduce
     -> NTT(own P-limbs).  x_local is [batch][q_count][N] in NTT form; the result is [batch][p_count][N]."""

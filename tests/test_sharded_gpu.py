@@ -82,7 +82,24 @@ def test_partial_scatter_matches_partial_plus_exchange(cuda_device, logn, l_in, 
         assert bool((bufs[r][world * batch * c * N:] == -1).all())         # nothing written past the window
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p", "p2p-groups2"])
+def test_ipc_comm_single_rank(cuda_device):
+    """mfhe_comm / mfhe_bconv_sharded_step with world = 1 (no peers to open): the C-ABI step equals the oracle."""
+    import torch
+    from matrix_fhe_gpu_b200 import sharded as S
+    logn, l_in, l_out, bits, batch = 12, 6, 4, 55, 3
+    N = 1 << logn
+    primes = [int(v) for v in O.get_primes(N, bits, l_in + l_out)]
+    q, p = primes[:l_in], primes[l_in:]
+    x = O.synth_polys(13, batch, q, N)
+    sh = S.LimbShardedBconv(logn, q, p, 0, 1)
+    comm = S.IpcComm(0, 1, l_out, N, batch)
+    for _ in range(3):                                   # both receive buffers, repeated epochs
+        got = comm.step(sh, torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
+        assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
+    comm.barrier(); torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p", "p2p-groups2", "ipc"])
 def test_limb_sharded_step_nccl(exchange):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:

@@ -29,7 +29,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--check", action="store_true")
-    ap.add_argument("--exchange", choices=["nccl", "pipelined", "p2p"], default="nccl",
+    ap.add_argument("--exchange", choices=["nccl", "pipelined", "p2p", "ipc"], default="nccl",
                     help="nccl: one all-to-all; pipelined: per batch group, overlapped; p2p: fused partial + peer stores")
     ap.add_argument("--groups", type=int, default=4)
     ap.add_argument("--p2p-groups", type=int, default=1, help="p2p: batch slices alternating between two streams")
@@ -70,8 +70,14 @@ def main():
             raise SystemExit("--exchange p2p needs torchrun with >= 2 ranks")
         sh.enable_p2p(a.batch)
 
+    ipc = None
+    if a.exchange == "ipc":
+        ipc = S.IpcComm(rank, world, a.lout, N, a.batch)      # mfhe_comm_*: CUDA IPC peers, C ABI only
+
     def step():
         work.copy_(x0)
+        if ipc is not None:
+            return ipc.step(sh, work, a.batch)
         if a.exchange == "p2p":
             return sh.step_p2p(work, a.batch, a.p2p_groups)
         if a.exchange == "pipelined":
@@ -112,6 +118,7 @@ def main():
                                                                          "batch": a.batch},
                           "exchange": {"kind": {"nccl": "all_to_all of partial sums (NCCL)",
                                                 "pipelined": "all_to_all per batch group (NCCL, async) overlapped with the transforms, groups=%d" % a.groups,
+                                                "ipc": "mfhe_bconv_sharded_step (C ABI): partial sums stored by the bconv kernel into the owners' CUDA-IPC receive buffers over NVLink, flag barrier",
                                                 "p2p": "partial sums stored by the bconv kernel into the owners' symmetric-memory buffers over NVLink, one device barrier, stream groups=%d" % a.p2p_groups}[a.exchange], "bytes_sent_per_rank": sent,
                                        "note": "GB/s below is an upper bound on link use: whole step time, not the collective alone",
                                        "gbs_per_rank_over_step": sent / (ms * 1e-3) / 1e9},
