@@ -18,9 +18,27 @@ typedef unsigned int u32;
 // {w, floor(w * 2^64 / q)} -- one 16-byte twiddle entry, one LDG.128.
 typedef ulonglong2 tw_t;
 
+#ifndef MFHE_CSUB_VARIANT
+#define MFHE_CSUB_VARIANT 2
+#endif
 __device__ __forceinline__ u64 csub(u64 x, u64 m) {       // x in [0, 2m) -> [0, m)
+#if MFHE_CSUB_VARIANT == 2
+    // The borrow of the 64-bit subtraction IS the predicate: IADD3 + IADD3.X (carry out) + 2 SEL = 4 ALU slots instead of
+    // the 6 of the compare form below (IADD3, IADD3.X, ISETP, ISETP.EX, SEL, SEL).  In the NTT row kernels a third of the
+    // ALU-pipe instructions are conditional subtracts, and ptxas balances the pipes by instruction COUNT -- it moves
+    // register copies and carry adds onto the fmaheavy pipe (IMAD.MOV, IMAD.X) when the ALU pipe is the fuller one, which
+    // is the pipe that binds these kernels -- so every ALU slot saved here also takes work off the multiplier pipe
+    // (cuobjdump, ntt_rows_fwd_kernel<16,2>: 1976 -> 1848 instructions, IMAD.MOV + IMAD.X 298 -> 203).
+    const u32 xl = (u32)x, xh = (u32)(x >> 32), ml = (u32)m, mh = (u32)(m >> 32);
+    u32 tl, th, b;
+    asm("sub.cc.u32 %0, %3, %5;\n\tsubc.cc.u32 %1, %4, %6;\n\tsubc.u32 %2, 0, 0;"
+        : "=r"(tl), "=r"(th), "=r"(b) : "r"(xl), "r"(xh), "r"(ml), "r"(mh));
+    tl = b ? xl : tl; th = b ? xh : th;
+    return ((u64)th << 32) | tl;
+#else
     u64 t = x - m;
     return t < x ? t : x;                                 // unsigned min trick: wraps when x < m
+#endif
 }
 
 // x * w mod q, lazily: any 64-bit x, result in [0, 2q).

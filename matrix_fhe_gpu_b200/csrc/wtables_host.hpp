@@ -11,17 +11,26 @@
 // matrix is unique, so the entries are identical mod q, and in fp64 the closed form evaluated in
 // long double is the correctly rounded inverse rather than one carrying elimination round-off.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <complex>
 #include <cstdint>
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "numth_host.hpp"
 
 namespace mfhe { namespace host {
+
+// table construction is a one-off burst: use the machine's cores even when the launcher exported OMP_NUM_THREADS=1
+// (torch.distributed.run does), capped so that eight ranks on one box do not oversubscribe badly
+inline int table_threads() {
+    const unsigned hw = std::thread::hardware_concurrency();
+    return (int)std::max(1u, std::min(hw ? hw : 1u, 16u));
+}
 
 inline u64 addmod(u64 a, u64 b, u64 q) { u64 s = a + b; return s >= q ? s - q : s; }
 inline u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }
@@ -76,7 +85,7 @@ inline void build_wcrt_limb(u64 q, int f, const std::vector<uint16_t>& wexp, con
     const size_t phi = wexp.size();
     V.assign(phi * phi, 0); Vinv.assign(phi * phi, 0);
     const u64 pinv = invmod((u64)p % q, q), ieta = invmod(eta, q);
-#pragma omp parallel for schedule(dynamic, 8)
+#pragma omp parallel for schedule(dynamic, 8) num_threads(table_threads())
     for (long w = 0; w < (long)phi; ++w) {
         u64 root = powmod(eta, wexp[w], q), cur = 1;
         for (size_t r = 0; r < phi; ++r) { V[(size_t)w * phi + r] = cur; cur = mulmod(cur, root, q); }
@@ -105,7 +114,7 @@ inline void build_wdft(int f, const std::vector<uint16_t>& wexp, const std::vect
     const size_t phi = wexp.size();
     const long double two_pi = 6.283185307179586476925286766559L;
     V.assign(phi * phi, cplx(0, 0)); Vinv.assign(phi * phi, cplx(0, 0));
-#pragma omp parallel for schedule(dynamic, 8)
+#pragma omp parallel for schedule(dynamic, 8) num_threads(table_threads())
     for (long w = 0; w < (long)phi; ++w) {
         std::vector<long double> gr((size_t)p), gi((size_t)p);
         for (size_t r = 0; r < phi; ++r) {
