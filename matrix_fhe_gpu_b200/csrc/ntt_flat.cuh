@@ -97,8 +97,11 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
                     const int jy = jx | (1 << tb);
                     if (b == LOGN - 1) {        // last stage: exact products, N^-1 folded in, canonical
                         const u64 t = v[p][jx] + c.q4 - v[p][jy], sum = v[p][jx] + v[p][jy];
-                        v[p][jx] = mul_shoup(sum, ninv, c.q);
-                        v[p][jy] = mul_shoup(t, w1n, c.q);
+                        // approximate quotient here too (3 wide + 2 high products instead of the ~7 wide ones of the
+                        // exact 64 x 64 high word): result < 4q for any 64-bit operand, two conditional subtracts
+                        // canonicalise (cuobjdump, ntt_cols_kernel<16,0,2>: IMAD.WIDE 269 -> 221)
+                        v[p][jx] = csub(csub(mul_shoup_lazy4(sum, ninv, c.nq), c.q2), c.q);
+                        v[p][jy] = csub(csub(mul_shoup_lazy4(t, w1n, c.nq), c.q2), c.q);
                     } else {
                         gs_bfly(v[p][jx], v[p][jy], w, c);
                     }
