@@ -70,6 +70,21 @@ def build_drivers():
         if r.returncode != 0:
             raise RuntimeError("drop-in build failed for " + rel + "\n" + r.stdout)
         built.append(exe)
+    # our own driver for the SURVEY 8(f) rank-1 row (same style, same link line; it includes ../include/...)
+    own = os.path.join(ROOT, "dropin", "drivers", "test_encrypted_matmul.cu")
+    d = os.path.join(OUT, "test")
+    os.makedirs(d, exist_ok=True)
+    link = os.path.join(d, "test_encrypted_matmul.cu")
+    if os.path.lexists(link):
+        os.remove(link)
+    os.symlink(own, link)
+    exe = os.path.join(OUT, "bin", "test_encrypted_matmul")
+    cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-w", link, "-o", exe, "-L" + PKG, "-lmatrix_fhe_shim", "-lmfhe_b200",
+           "-Xlinker", "-rpath=$ORIGIN/../../../matrix_fhe_gpu_b200"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("drop-in build failed for test_encrypted_matmul.cu\n" + r.stdout)
+    built.append(exe)
     return built
 
 

@@ -35,18 +35,22 @@ __device__ __forceinline__ void mma_u8_t(int (&c)[4], const u32 (&a)[4], u32 b0,
 template <int ND, bool NEG, bool TR>
 __device__ __forceinline__ void stage_digits(unsigned char* dst, const u64* __restrict__ src, int koff, u64 q) {
     if constexpr (TR) {
+        // lanes run along the rows (the source's contiguous axis: 256-byte segments per warp and k), a thread gathers the
+        // four consecutive k of one row and stores them as one 32-bit word per digit plane
 #pragma unroll
         for (int r = 0; r < TN * TN / 4 / TTH; ++r) {
-            const int id = threadIdx.x + TTH * r, k = id >> 4, quad = id & 15;
-            const ulonglong2 v01 = *reinterpret_cast<const ulonglong2*>(src + k * TN + quad * 4);
-            const ulonglong2 v23 = *reinterpret_cast<const ulonglong2*>(src + k * TN + quad * 4 + 2);
-            u64 x[4] = {v01.x, v01.y, v23.x, v23.y};
+            const int row = threadIdx.x & (TN - 1), kq = (threadIdx.x >> 6) + (TTH / TN) * r;
+            u64 x[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (NEG) x[j] = q - x[j];
-                unsigned char* d = dst + (quad * 4 + j) * TRS + koff + k;
+            for (int j = 0; j < 4; ++j) { x[j] = src[(4 * kq + j) * TN + row]; if (NEG) x[j] = q - x[j]; }
+            unsigned char* d = dst + row * TRS + koff + kq * 4;
 #pragma unroll
-                for (int v = 0; v < ND; ++v) d[v * TN * TRS] = (unsigned char)(x[j] >> (8 * v));
+            for (int v = 0; v < ND; ++v) {
+                const int sh = v < 4 ? 0 : 32;
+                const u32 sel = (u32)(v & 3) | ((u32)(4 + (v & 3)) << 4);
+                const u32 t01 = __byte_perm((u32)(x[0] >> sh), (u32)(x[1] >> sh), sel);
+                const u32 t23 = __byte_perm((u32)(x[2] >> sh), (u32)(x[3] >> sh), sel);
+                *reinterpret_cast<u32*>(d + v * TN * TRS) = __byte_perm(t01, t23, 0x5410);
             }
         }
         return;

@@ -102,6 +102,14 @@ def test_wcrt_roundtrip_driver_matches_our_kernels_and_exact_integers(cuda_devic
     assert centred == int(rt[worst]) and abs(int(v[worst]) - centred) == max_err
 
 
+def test_encrypted_matmul_driver(cuda_device):
+    """dropin/drivers/test_encrypted_matmul.cu (ours, in the style of the reference's drivers): reference C++ API for
+    init / keygen / encode / encrypt_pair, C ABI for the twist, the ciphertext product and its decryption; exit code 0
+    iff max_err <= 2^-20 * max|entry| over all 512 lanes."""
+    r = run("test_encrypted_matmul", cuda_device)
+    assert r.returncode == 0 and "[SUCCESS]" in r.stdout, r.stdout[-2000:]
+
+
 def test_stale_drivers_print_what_the_reference_would(cuda_device):
     """The two drivers without a CMake target.  test/tmp.cu is an older copy of main.cu: same pipeline, must SUCCEED with
     max_err < 1e-4.  test/test_encode_decode_loop.cu is stale in the reference itself: it decodes
