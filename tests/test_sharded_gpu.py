@@ -82,6 +82,21 @@ def test_partial_scatter_matches_partial_plus_exchange(cuda_device, logn, l_in, 
         assert bool((bufs[r][world * batch * c * N:] == -1).all())         # nothing written past the window
 
 
+@pytest.mark.parametrize("logn,l_in,l_out,bits,batch", [(12, 48, 4, 55, 2), (12, 32, 3, 55, 1), (12, 7, 3, 58, 2)])
+def test_unsharded_step_windows(cuda_device, logn, l_in, l_out, bits, batch):
+    """world = 1: the conversion of a wide base runs window by window on the register-resident kernel forms (48 = 2 x 24,
+    32 = 2 x 16) + mfhe_bconv_reduce, a base without such a split (7) through one mfhe_bconv: both equal the oracle."""
+    import torch
+    from matrix_fhe_gpu_b200 import sharded as S
+    N = 1 << logn
+    primes = [int(v) for v in O.get_primes(N, bits, l_in + l_out)]
+    q, p = primes[:l_in], primes[l_in:]
+    x = O.synth_polys(17, batch, q, N)
+    sh = S.LimbShardedBconv(logn, q, p, 0, 1)
+    got = sh.step_unsharded(torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
+    assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
+
+
 def test_ipc_comm_single_rank(cuda_device):
     """mfhe_comm / mfhe_bconv_sharded_step with world = 1 (no peers to open): the C-ABI step equals the oracle."""
     import torch
