@@ -140,6 +140,9 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
             out[tag] = {"ms_per_batch": timed(loop, 3), "encode_ms": timed(lambda: g.encode_to_wntt_eval(m), 3),
                         "decrypt_decode_ms": timed(lambda: g.decrypt_and_decode(ct_r, ct_i, zero, dec), 3),
                         "batch": "512 lanes x 64x64 complex fp64 (2^21 values)", "max_err": err,
+                        "pipeline_pair_ms": timed(lambda: (g.encode_encrypt_pair(m, sk, cr, ci), g.decrypt_and_decode(cr, ci, sk, dec)), 3),
+                        "pipeline_pair_three_calls_ms": timed(lambda: (g.encrypt_pair(*g.encode_to_wntt_eval(m), sk, cr, ci),
+                                                                       g.decrypt_and_decode(cr, ci, sk, dec)), 3),
                         "context_create_ms": t_ctx,
                         "context_create_note": "mfhe_ctx_create: W-CRT tables built on the device (wtables_gpu.cu); the "
                                                "reference's init_he_backend is baselines.reference_cuda.init_he_backend_ms"}
