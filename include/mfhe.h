@@ -303,6 +303,9 @@ void mfhe_comm_destroy(mfhe_comm *comm);
 int mfhe_comm_export(const mfhe_comm *comm, void *h_handle /* MFHE_COMM_HANDLE_BYTES */);
 int mfhe_comm_import(mfhe_comm *comm, const void *h_all_handles /* world x MFHE_COMM_HANDLE_BYTES, rank order */);
 int mfhe_comm_barrier(mfhe_comm *comm, void *stream);            /* stream-ordered, release / acquire at system scope */
+/* batch slices per step (default 1): with g > 1 the step is software-pipelined -- slice s's reduce + NTT run on a side stream
+ * while slice s+1's INTT and NVLink-bound scatter run on the caller's stream, one barrier per slice */
+int mfhe_comm_set_groups(mfhe_comm *comm, int groups);
 /* INTT(own Q-limbs) -> partial sums stored into the owners' receive buffers -> barrier -> reduce -> NTT(own P-limbs).
  * plan_q / plan_p / bconv cover the FULL bases; d_x_local [batch][q_count][N] (destroyed), d_out [batch][p_count][N];
  * rank r owns the r-th balanced contiguous window of each base (Phantom: nwt_2d_radix8_backward_inplace + bConv_BEHZ +
@@ -354,6 +357,9 @@ int mfhe_bconv_partial_scatter(const mfhe_bconv_plan *plan, const uint64_t *d_in
  * [out_start, out_start+out_count) */
 int mfhe_bconv_reduce(const mfhe_bconv_plan *plan, const uint64_t *d_parts, int nparts, int out_start, int out_count,
                       uint64_t *d_out, size_t N, size_t batch, void *stream);
+/* the same on a batch slice of a larger [nparts][batch][count][N] buffer: part_stride words between consecutive parts */
+int mfhe_bconv_reduce_strided(const mfhe_bconv_plan *plan, const uint64_t *d_parts, int nparts, size_t part_stride,
+                              int out_start, int out_count, uint64_t *d_out, size_t N, size_t batch, void *stream);
 
 #ifdef __cplusplus
 }

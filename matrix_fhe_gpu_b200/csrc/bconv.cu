@@ -142,12 +142,12 @@ bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_
 
 __global__ void bconv_reduce_kernel(const u64* __restrict__ parts, u64* __restrict__ out, size_t per_part, int nparts,
                                     size_t N, int out_start, int out_count, const u64* __restrict__ p,
-                                    const ulonglong2* __restrict__ mu_p) {
+                                    const ulonglong2* __restrict__ mu_p, size_t part_stride) {
     const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= per_part) return;
     const int j = out_start + (int)((idx / N) % out_count);
     u64 s = 0;
-    for (int k = 0; k < nparts; ++k) s += parts[(size_t)k * per_part + idx];      // nparts * p_j < 2^64
+    for (int k = 0; k < nparts; ++k) s += parts[(size_t)k * part_stride + idx];      // nparts * p_j < 2^64
     out[idx] = reduce64(s, p[j], mu_p[j].y);
 }
 }  // namespace
@@ -220,15 +220,13 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     if (in_start < 0 || in_count < 1 || in_start + in_count > b->l_in) return fail(MFHE_EINVAL, std::string(who) + ": limb window out of range");
     if (!N || !batch) return MFHE_OK;
     if (batch > 65535) return fail(MFHE_EINVAL, std::string(who) + ": batch too large");
-    static bool attr_set = false;
-    if (!attr_set) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaSuccess;
         const void* fns[4] = {(const void*)bconv_kernel<false, false, 0>, (const void*)bconv_kernel<false, true, 0>,
                               (const void*)bconv_kernel<true, false, 0>, (const void*)bconv_kernel<true, true, 0>};
         for (const void* f : fns)
             if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, who);
-        attr_set = true;
     }
     dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
     // one-word Barrett iff sum_i y_i c_i < in_count * qmax * p_j < 2^(k_j + 61) for every j: in_count * qmax <= 2^61
@@ -287,14 +285,23 @@ extern "C" int mfhe_bconv_partial_scatter(const mfhe_bconv_plan* b, const uint64
     }
     return bconv_run(b, in, in_start, in_count, nullptr, N, batch, s, "bconv_partial_scatter", &sc);
 }
-extern "C" int mfhe_bconv_reduce(const mfhe_bconv_plan* b, const uint64_t* parts, int nparts, int out_start, int out_count,
-                                 uint64_t* out, size_t N, size_t batch, void* s) {
-    if (!b || !parts || !out || nparts < 1 || nparts > 8 || out_start < 0 || out_count < 1 || out_start + out_count > b->l_out)
+// part_stride: words between consecutive parts (>= batch * out_count * N; a batch slice of a [nparts][batch][count][N] buffer)
+extern "C" int mfhe_bconv_reduce_strided(const mfhe_bconv_plan* b, const uint64_t* parts, int nparts, size_t part_stride,
+                                         int out_start, int out_count, uint64_t* out, size_t N, size_t batch, void* s) {
+    if (!b || !parts || !out || nparts < 1 || out_start < 0 || out_count < 1 || out_start + out_count > b->l_out)
         return fail(MFHE_EINVAL, "bconv_reduce: bad argument");
+    uint64_t pmax = 0;
+    for (int j = out_start; j < out_start + out_count; ++j) pmax = std::max(pmax, b->p[j]);
+    if ((unsigned __int128)pmax * (unsigned)nparts >> 64) return fail(MFHE_EINVAL, "bconv_reduce: nparts * p_j must stay below 2^64");
     const size_t per = batch * (size_t)out_count * N;
     if (!per) return MFHE_OK;
+    if (part_stride < per) return fail(MFHE_EINVAL, "bconv_reduce: part stride smaller than a part");
     bconv_reduce_kernel<<<(unsigned)((per + 255) / 256), 256, 0, (cudaStream_t)s>>>((const u64*)parts, (u64*)out, per, nparts, N,
-                                                                                  out_start, out_count, b->d_p, b->d_mu_p);
+                                                                                  out_start, out_count, b->d_p, b->d_mu_p, part_stride);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "bconv_reduce");
+}
+extern "C" int mfhe_bconv_reduce(const mfhe_bconv_plan* b, const uint64_t* parts, int nparts, int out_start, int out_count,
+                                 uint64_t* out, size_t N, size_t batch, void* s) {
+    return mfhe_bconv_reduce_strided(b, parts, nparts, batch * (size_t)out_count * N, out_start, out_count, out, N, batch, s);
 }

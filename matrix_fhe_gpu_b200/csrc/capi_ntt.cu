@@ -29,6 +29,7 @@ extern "C" void mfhe_ntt_plan_destroy(mfhe_ntt_plan* p) {
     if (!p) return;
     cudaFree(p->d_moduli); cudaFree(p->d_tw); cudaFree(p->d_itw);
     cudaFree(p->d_ninv); cudaFree(p->d_w1n); cudaFree(p->d_stage); cudaFree(p->d_mu);
+    for (cudaStream_t st : p->host_streams) if (st) cudaStreamDestroy(st);
     delete p;
 }
 
@@ -153,7 +154,7 @@ static int run_host(mfhe_ntt_plan* p, bool fwd, uint64_t* h, size_t batch) {
         if ((e = cudaMalloc((void**)&p->d_stage, bytes)) != cudaSuccess) return cuda_fail(e, "ntt_host staging");
         p->stage_bytes = bytes;
     }
-    static cudaStream_t st[3] = {nullptr, nullptr, nullptr};
+    cudaStream_t* st = p->host_streams;          // owned by the plan (a plan belongs to one device)
     if (!st[0])
         for (int i = 0; i < 3; ++i)
             if ((e = cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking)) != cudaSuccess) return cuda_fail(e, "ntt_host stream");

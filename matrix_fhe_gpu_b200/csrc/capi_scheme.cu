@@ -815,7 +815,12 @@ extern "C" int mfhe_apply_gl_perm(const uint64_t* in, uint64_t* out, int limbs, 
         return fail(MFHE_EINVAL, "apply_gl_perm: bad argument");
     // tables are tiny: keep one device copy per n for the life of the process (the reference keeps
     // d_gl_perm / d_gl_inv_perm the same way, ntt_core.cu:16-18)
-    static uint32_t* d_tab[13][2] = {};
+    static uint32_t* d_tabs[16][13][2] = {};                // per device
+    static std::mutex tab_mu;
+    int dev = 0; cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 16) return fail(MFHE_EUNSUPPORTED, "apply_gl_perm: device ordinal above 15");
+    std::lock_guard<std::mutex> lk(tab_mu);
+    auto& d_tab = d_tabs[dev];
     int logn = 0; while ((1 << logn) < n) ++logn;
     if (!d_tab[logn][0]) {
         std::vector<uint32_t> p(n), ip(n);

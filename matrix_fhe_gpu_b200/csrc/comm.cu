@@ -30,6 +30,9 @@ struct mfhe_comm {
     bool imported = false;
     unsigned long long epoch = 0;
     int phase = 0;
+    int groups = 1;
+    cudaStream_t side = nullptr;                         // reduce + NTT of slice s next to INTT + scatter of slice s+1
+    cudaEvent_t ev_bar[16] = {}, ev_done = nullptr;
 };
 
 namespace {
@@ -61,6 +64,9 @@ extern "C" void mfhe_comm_destroy(mfhe_comm* c) {
         cudaIpcCloseMemHandle(c->peer_recv[0][r]); cudaIpcCloseMemHandle(c->peer_recv[1][r]); cudaIpcCloseMemHandle(c->peer_flags[r]);
     }
     cudaFree(c->recv[0]); cudaFree(c->recv[1]); cudaFree(c->flags);
+    if (c->side) cudaStreamDestroy(c->side);
+    for (cudaEvent_t e : c->ev_bar) if (e) cudaEventDestroy(e);
+    if (c->ev_done) cudaEventDestroy(c->ev_done);
     delete c;
 }
 
@@ -118,6 +124,18 @@ extern "C" int mfhe_comm_barrier(mfhe_comm* c, void* stream) {
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "comm_barrier");
 }
 
+extern "C" int mfhe_comm_set_groups(mfhe_comm* c, int groups) {
+    if (!c || groups < 1 || groups > 16) return fail(MFHE_EINVAL, "comm_set_groups: 1..16 slices");
+    if (groups > 1 && !c->side) {
+        cudaError_t e = cudaStreamCreateWithFlags(&c->side, cudaStreamNonBlocking);
+        for (int i = 0; i < 16 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_bar[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming);
+        if (e != cudaSuccess) return cuda_fail(e, "comm_set_groups");
+    }
+    c->groups = groups;
+    return MFHE_OK;
+}
+
 extern "C" size_t mfhe_bconv_sharded_recv_words(int world, int l_out, size_t N, size_t batch) {
     int s = 0, cmax = 0;
     for (int r = 0; r < world; ++r) { int c; window(l_out, world, r, &s, &c); cmax = std::max(cmax, c); }
@@ -142,9 +160,7 @@ extern "C" int mfhe_bconv_sharded_step(mfhe_comm* c, const mfhe_ntt_plan* plan_q
     window(l_in, c->world, c->rank, &qs, &qc);
     window(l_out, c->world, c->rank, &ps, &pc);
     const int ph = c->phase; c->phase ^= 1;
-    int rc = mfhe_ntt_inverse_limbs(plan_q, d_x_local, batch, qs, qc, stream);
-    if (rc != MFHE_OK) return rc;
-    std::vector<uint64_t*> dst(l_out); std::vector<size_t> stride(l_out);
+    std::vector<uint64_t*> dst(l_out), dsl(l_out); std::vector<size_t> stride(l_out);
     for (int r = 0; r < c->world; ++r) {
         int s, cnt; window(l_out, c->world, r, &s, &cnt);
         for (int j = s; j < s + cnt; ++j) {
@@ -152,9 +168,36 @@ extern "C" int mfhe_bconv_sharded_step(mfhe_comm* c, const mfhe_ntt_plan* plan_q
             stride[j] = (size_t)cnt * N;
         }
     }
-    rc = mfhe_bconv_partial_scatter(bc, d_x_local, qs, qc, dst.data(), stride.data(), N, batch, stream);
-    if (rc == MFHE_OK) rc = mfhe_comm_barrier(c, stream);
-    if (rc == MFHE_OK) rc = mfhe_bconv_reduce(bc, (const uint64_t*)c->recv[ph], c->world, ps, pc, d_out, N, batch, stream);
-    if (rc == MFHE_OK) rc = mfhe_ntt_forward_limbs(plan_p, d_out, batch, ps, pc, stream);
+    const int G = (int)std::min<size_t>((size_t)c->groups, batch);
+    int rc = MFHE_OK;
+    if (G <= 1) {
+        rc = mfhe_ntt_inverse_limbs(plan_q, d_x_local, batch, qs, qc, stream);
+        if (rc == MFHE_OK) rc = mfhe_bconv_partial_scatter(bc, d_x_local, qs, qc, dst.data(), stride.data(), N, batch, stream);
+        if (rc == MFHE_OK) rc = mfhe_comm_barrier(c, stream);
+        if (rc == MFHE_OK) rc = mfhe_bconv_reduce(bc, (const uint64_t*)c->recv[ph], c->world, ps, pc, d_out, N, batch, stream);
+        if (rc == MFHE_OK) rc = mfhe_ntt_forward_limbs(plan_p, d_out, batch, ps, pc, stream);
+        return rc;
+    }
+    // software pipeline over batch slices: the caller's stream does INTT -> scatter -> barrier per slice, the side stream
+    // reduce -> NTT of a slice as soon as its barrier has passed; the caller's stream rejoins at the end
+    cudaStream_t st = (cudaStream_t)stream;
+    for (int g = 0; g < G && rc == MFHE_OK; ++g) {
+        const size_t b0 = batch * g / G, nb = batch * (g + 1) / G - b0;
+        if (!nb) continue;
+        uint64_t* xs = d_x_local + b0 * (size_t)qc * N;
+        for (int j = 0; j < l_out; ++j) dsl[j] = dst[j] + b0 * stride[j];
+        rc = mfhe_ntt_inverse_limbs(plan_q, xs, nb, qs, qc, stream);
+        if (rc == MFHE_OK) rc = mfhe_bconv_partial_scatter(bc, xs, qs, qc, dsl.data(), stride.data(), N, nb, stream);
+        if (rc == MFHE_OK) rc = mfhe_comm_barrier(c, stream);
+        if (rc != MFHE_OK) break;
+        cudaEventRecord(c->ev_bar[g], st);
+        cudaStreamWaitEvent(c->side, c->ev_bar[g], 0);
+        uint64_t* os = d_out + b0 * (size_t)pc * N;
+        rc = mfhe_bconv_reduce_strided(bc, (const uint64_t*)c->recv[ph] + b0 * (size_t)pc * N, c->world, batch * (size_t)pc * N, ps, pc,
+                                       os, N, nb, c->side);
+        if (rc == MFHE_OK) rc = mfhe_ntt_forward_limbs(plan_p, os, nb, ps, pc, c->side);
+    }
+    cudaEventRecord(c->ev_done, c->side);
+    cudaStreamWaitEvent(st, c->ev_done, 0);
     return rc;
 }

@@ -596,11 +596,9 @@ xy_sandwich_dmma64_kernel(const double2* __restrict__ A, const double2* __restri
 static cudaError_t xy_sandwich_dmma64_launch(const double2* A, const double2* B, const double2* in, double2* out, int lanes,
                                              cudaStream_t st) {
     constexpr size_t smem = (size_t)64 * (XSA + XSM) * sizeof(double);
-    static bool attr_set = false;
-    if (!attr_set) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaFuncSetAttribute(xy_sandwich_dmma64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     xy_sandwich_dmma64_kernel<<<lanes, 256, smem, st>>>(A, B, in, out);
     return cudaGetLastError();
@@ -611,11 +609,9 @@ static cudaError_t xy_sandwich_launch_r(const double2* A, const double2* B, cons
                                         cudaStream_t st) {
     constexpr int n = 16 * R;
     constexpr size_t smem = 2 * (size_t)n * n * sizeof(double2);
-    static bool attr_set = false;
-    if (!attr_set) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaFuncSetAttribute(xy_sandwich_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     xy_sandwich_kernel<R><<<lanes, 256, smem, st>>>(A, B, in, out);
     return cudaGetLastError();

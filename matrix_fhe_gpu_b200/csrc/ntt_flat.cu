@@ -264,11 +264,9 @@ static cudaError_t launch_pair(bool fwd, u64* data, const NttTables& T, int limb
                                size_t polys, cudaStream_t st, const u64* mul, const ulonglong2* mu) {
     constexpr int LOGR = LOGN - 8;
     constexpr size_t col_smem = (size_t)PB * 4096 * sizeof(u64);
-    static bool attr_done = false;
-    if (!attr_done) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaFuncSetAttribute(ntt_cols_kernel<LOGN, true, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem);
         cudaFuncSetAttribute(ntt_cols_kernel<LOGN, false, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)col_smem);
-        attr_done = true;
     }
     const unsigned gy = (unsigned)(polys / PB) * (unsigned)limb_count;
     dim3 gc(256 / (4096 >> LOGR), gy);

@@ -17,6 +17,7 @@ struct mfhe_ntt_plan {
     size_t chunk = 0;
     uint64_t* d_stage = nullptr;               // staging for the *_host entry points
     size_t stage_bytes = 0;
+    cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};   // H2D / compute / D2H of the *_host entry points (lazy)
     NttTables flat() const { return NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L}; }
     SmallTables small() const {
         return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention};

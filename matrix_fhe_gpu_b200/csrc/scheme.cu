@@ -296,11 +296,9 @@ cudaError_t trace_gemm_launch(const u64* Ar, const u64* Ai, const u64* Bpr, cons
                               int transposed) {
     const size_t smem = 4 * (size_t)n * (n + 1) * sizeof(u64);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
-    static bool attr_set = false;
-    if (!attr_set) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaFuncSetAttribute(trace_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     trace_gemm_kernel<<<(unsigned)(batch * limbs), 256, smem, st>>>(Ar, Ai, Bpr, Bpi, Cr, Ci, moduli, mu, n, limbs, transposed);
     return cudaGetLastError();

@@ -177,11 +177,9 @@ wcrt_tc_kernel(const WcrtArgs a) {
 template <int SRC, int ND>
 static cudaError_t launch_nd(const WcrtArgs& a, cudaStream_t st) {
     constexpr int smem = 2 * ND * (MC + NC) * RS;
-    static bool attr = false;
-    if (!attr) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaFuncSetAttribute(wcrt_tc_kernel<SRC, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        attr = true;
     }
     dim3 grid(a.cols / NC, a.phi / MC, a.lzn);
     wcrt_tc_kernel<SRC, ND><<<grid, TCT, smem, st>>>(a);

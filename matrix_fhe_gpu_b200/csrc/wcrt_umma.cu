@@ -441,14 +441,12 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
 template <int SRC, int ND>
 static cudaError_t launch_umma_nd(const WcrtArgs& a, cudaStream_t st) {
     using C = UmmaCfg<ND, SRC>;
-    static bool attr = false;
-    if (!attr) {
+    {   // set on every call: cheap, and right for any device / thread (no process-wide one-shot flag)
         cudaError_t e = cudaFuncSetAttribute(wcrt_umma_kernel<SRC, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) return e;
-        attr = true;
     }
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+    int sms = 0, dev = 0;
+    cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int ntiles = ((a.cols + C::UN - 1) / C::UN) * (a.phi / UM) * a.lzn;
     wcrt_umma_kernel<SRC, ND><<<ntiles < sms ? ntiles : sms, C::THREADS, C::SMEM, st>>>(a, ntiles);
     return cudaGetLastError();

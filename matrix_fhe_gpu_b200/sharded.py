@@ -121,6 +121,7 @@ class IpcComm:
         L.mfhe_comm_import.argtypes = [C.c_void_p, C.c_void_p]
         L.mfhe_comm_barrier.argtypes = [C.c_void_p, C.c_void_p]
         L.mfhe_bconv_sharded_step.argtypes = [C.c_void_p] * 6 + [C.c_size_t, C.c_void_p]
+        L.mfhe_comm_set_groups.argtypes = [C.c_void_p, C.c_int]
         self._L, self.rank, self.world = L, rank, world
         words = L.mfhe_bconv_sharded_recv_words(world, l_out, n, batch)
         h = C.c_void_p()
@@ -148,6 +149,11 @@ class IpcComm:
         from . import check, _stream_handle
         check(self._L.mfhe_comm_barrier(self._h, _stream_handle()))
 
+    def set_groups(self, groups: int):
+        """Batch slices per step: > 1 overlaps a slice's reduce + NTT (side stream) with the next slice's INTT + scatter."""
+        from . import check
+        check(self._L.mfhe_comm_set_groups(self._h, groups))
+
     def step(self, sh: "LimbShardedBconv", x_local, batch: int):
         """mfhe_bconv_sharded_step: the whole config-5 step of this rank in one C call."""
         import torch
@@ -170,6 +176,9 @@ class LimbShardedBconv:
         self.rank, self.world, self.group = rank, world, group
         self.q = [int(v) for v in q_in]
         self.p = [int(v) for v in p_out]
+        if world > len(self.q) or world > len(self.p):
+            raise ValueError(f"limb sharding needs at least one limb of each base per rank: world = {world}, "
+                             f"|Q| = {len(self.q)}, |P| = {len(self.p)}")
         self.q_windows = limb_windows(len(self.q), world)
         self.p_windows = limb_windows(len(self.p), world)
         self.plan_q = NttPlan(logn, self.q)

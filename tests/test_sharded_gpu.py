@@ -112,19 +112,28 @@ def test_ipc_comm_single_rank(cuda_device):
         got = comm.step(sh, torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
         assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
     comm.barrier(); torch.cuda.synchronize()
+    for groups in (2, 3, 16):                            # sliced pipeline (side stream, strided reduce); 16 > batch clamps to 3
+        comm.set_groups(groups)
+        for _ in range(3):
+            got = comm.step(sh, torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
+            assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
+    with pytest.raises(RuntimeError):
+        comm.set_groups(0)
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p", "p2p-groups2", "ipc"])
+@pytest.mark.parametrize("exchange", ["nccl", "pipelined", "p2p", "p2p-groups2", "ipc", "ipc-groups"])
 def test_limb_sharded_step_nccl(exchange):
     import torch
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", "29631", os.path.join(ROOT, "tools", "run_sharded.py"), "--logn", "13", "--lin", "6", "--lout", "4",
-           "--batch", "3" if exchange in ("pipelined", "p2p-groups2") else "2", "--check", "--steps", "3",
+           "--batch", "3" if exchange in ("pipelined", "p2p-groups2", "ipc-groups") else "2", "--check", "--steps", "3",
            "--exchange", exchange.split("-")[0]]
     if exchange == "p2p-groups2":        # the two-stream form behind the config-5 number; a batch that does not divide evenly
         cmd += ["--p2p-groups", "2"]
+    if exchange == "ipc-groups":         # mfhe_comm_set_groups: sliced software pipeline of the C-ABI step, uneven slices
+        cmd += ["--ipc-groups", "2,3"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "parity ok" in r.stdout

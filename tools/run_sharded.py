@@ -33,6 +33,7 @@ def main():
                     help="nccl: one all-to-all; pipelined: per batch group, overlapped; p2p: fused partial + peer stores")
     ap.add_argument("--groups", type=int, default=4)
     ap.add_argument("--p2p-groups", type=int, default=1, help="p2p: batch slices alternating between two streams")
+    ap.add_argument("--ipc-groups", default="", help="ipc: comma list of batch-slice counts to time after the first pass (mfhe_comm_set_groups)")
     ap.add_argument("--also-p2p-groups", type=int, default=0,
                     help="p2p: after the main measurement, time the step again with this many stream groups (second JSON line)")
     a = ap.parse_args()
@@ -147,6 +148,33 @@ def main():
             print(json.dumps({"metric": "limb_sharded_intt_bconv_ntt_polys_per_s", "value": a.batch / (float(t.item()) * 1e-3),
                               "unit": "polys/s", "n_gpus": world, "ms_per_step": float(t.item()), "p2p_stream_groups": a.p2p_groups,
                               "parity": ("ok" if ok2 else "FAILED") if a.check else "not checked"}))
+    if ipc is not None and a.ipc_groups:
+        for g in [int(v) for v in a.ipc_groups.split(",")]:
+            ipc.set_groups(g)
+            for _ in range(max(a.warmup, 1)):
+                out = step()
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            ev[0].record()
+            for _ in range(a.steps):
+                out = step()
+            ev[1].record(); torch.cuda.synchronize()
+            t = torch.tensor([ev[0].elapsed_time(ev[1]) / a.steps], device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            okg = True
+            if a.check:
+                okg = bool((out.cpu().numpy().view(np.uint64) == want).all())
+                flag = torch.tensor([1 if okg else 0], device=dev)
+                if world > 1:
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                okg = bool(flag.item())
+                ok = ok and okg
+            if rank == 0:
+                print(json.dumps({"metric": "limb_sharded_intt_bconv_ntt_polys_per_s", "value": a.batch / (float(t.item()) * 1e-3),
+                                  "unit": "polys/s", "n_gpus": world, "ms_per_step": float(t.item()), "ipc_batch_slices": g,
+                                  "parity": ("ok" if okg else "FAILED") if a.check else "not checked"}))
     if world > 1:
         dist.destroy_process_group()
     if not ok:
