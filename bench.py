@@ -194,6 +194,57 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
     return out
 
 
+def config2_50bit_block(dev, steps=20):
+    """SURVEY config 2's secondary run: the headline shape on 50-bit primes.  Moduli below 2^50 let the butterflies run on
+    the FP64 pipe (csrc/modmath.cuh); the integer kernels are timed on the same plan beside it."""
+    import torch
+    import matrix_fhe_gpu_b200 as m
+    import oracle as O
+    mods = O.coeff_modulus_create(N, 50, LIMBS)
+    plan = m.NttPlan(LOGN, mods)
+    x = O.synth_polys(43, BATCH, mods, N)
+    d = torch.from_numpy(x.view(np.int64)).to(dev)
+    stream = torch.cuda.current_stream()
+    peak, _ = peaks()
+    out = {"workload": WORKLOAD.replace("60-bit", "50-bit"), "default_arith": "fp64" if plan.arith == 1 else "int"}
+
+    def timed(chunk):
+        plan.set_chunk(chunk)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        tf, ti = [], []
+        for i in range(steps + 3):
+            ev[0].record(stream); plan.forward_(d, stream)
+            ev[1].record(stream); plan.inverse_(d, stream)
+            ev[2].record(stream); torch.cuda.synchronize()
+            if i >= 3:
+                tf.append(ev[0].elapsed_time(ev[1])); ti.append(ev[1].elapsed_time(ev[2]))
+        return statistics.median(tf), statistics.median(ti)
+
+    for name, arith in (("fp64", 1), ("int", 0)):
+        if arith == 1 and plan.arith != 1:
+            try:
+                plan.set_arith(1)
+            except Exception as e:                       # noqa: BLE001
+                out[name] = {"error": repr(e)[:200]}
+                continue
+        plan.set_arith(arith)
+        tf, ti = timed(0)
+        blk = {"ms_forward": tf, "ms_inverse": ti, "limb_polys_per_s": LIMB_POLYS / ((tf + ti) * 1e-3),
+               "hbm_frac": ALGO_BYTES_PER_TRANSFORM * LIMB_POLYS / (max(tf, ti) * 1e-3) / 1e9 / peak}
+        if arith == 1:                                   # with a cheaper butterfly the L2-resident second pass can pay
+            chunks = {}
+            for c in (128, 256, 512):
+                cf, ci = timed(c)
+                chunks[str(c)] = LIMB_POLYS / ((cf + ci) * 1e-3)
+            blk["chunk_limb_polys_ab"] = chunks
+        out[name] = blk
+    plan.set_chunk(0)
+    assert (d[0].cpu().numpy().view(np.uint64) == x[0]).all(), "50-bit round trip failed"
+    out["note"] = ("same results word for word (tests/test_ntt_fp64_gpu.py); Phantom on the same primes: "
+                   "baselines.phantom.cfg2_50bit_limb_poly_pairs_per_s")
+    return out
+
+
 def gpu_baselines():
     """The two GPU baselines BASELINE.json's north_star names, timed on THIS box in THIS run: the reference's own CUDA
     kernels and Phantom's, i.e. the UNMODIFIED sources of /root/reference compiled for sm_100a by baseline/build_ref.py
@@ -603,6 +654,11 @@ def main():
         del d
         torch.cuda.empty_cache()
         secondary = secondary_metrics(dev, world, dist if world > 1 else None, with_cpu=(rank == 0 and world == 1 and not args.no_cpu))
+        if rank == 0:
+            try:
+                secondary["config2_50bit_primes"] = config2_50bit_block(dev)
+            except Exception as e:                          # noqa: BLE001
+                secondary["config2_50bit_primes"] = {"error": repr(e)[:400]}
         if not args.no_config5:
             try:
                 secondary["config5_limb_sharded"] = config5_block(dev, world, rank, dist if world > 1 else None)

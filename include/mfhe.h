@@ -97,6 +97,14 @@ int mfhe_ntt_inverse_host(mfhe_ntt_plan *plan, uint64_t *h_data, size_t batch);
  * intermediate stays in L2 (0 = whole batch in one pair of launches). */
 int mfhe_ntt_plan_set_chunk(mfhe_ntt_plan *plan, size_t chunk_limb_polys);
 
+/* Arithmetic of the flat transforms (N = 2^12..2^17).  0: 64-bit integer butterflies (any modulus below 2^60).
+ * 1: butterflies on the FP64 pipe -- exact, same results word for word -- available when every modulus of the plan is
+ * below 2^50 (SURVEY config 2's 50-bit run, the 35/45-bit moduli of the matrix scheme) and then the default; inputs
+ * must be below 2q.  MFHE_NTT_ARITH=int in the environment keeps new plans on 0.  set_arith returns MFHE_EUNSUPPORTED
+ * when 1 is asked of a plan that cannot run it. */
+int mfhe_ntt_plan_arith(const mfhe_ntt_plan *plan);
+int mfhe_ntt_plan_set_arith(mfhe_ntt_plan *plan, int arith);
+
 /* Pointwise ops on [batch][L][N] in the plan's moduli (canonical in, canonical out).
  * Replaces pointwise_mul kernels of the reference (src/core/HE.cu:509-531 semantics with
  * a full-size second operand) and Phantom's multiply_rns_poly. */

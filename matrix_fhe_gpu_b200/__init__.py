@@ -51,6 +51,8 @@ def lib() -> C.CDLL:
         L.mfhe_ntt_plan_root.argtypes = [_vp, C.c_int]
         L.mfhe_ntt_plan_get_table.argtypes = [_vp, C.c_int, C.c_int, _vp, _vp]
         L.mfhe_ntt_plan_set_chunk.argtypes = [_vp, C.c_size_t]
+        L.mfhe_ntt_plan_arith.argtypes = [_vp]
+        L.mfhe_ntt_plan_set_arith.argtypes = [_vp, C.c_int]
         for name in ("mfhe_ntt_forward", "mfhe_ntt_inverse"):
             getattr(L, name).restype = C.c_int
             getattr(L, name).argtypes = [_vp, _vp, C.c_size_t, _vp]
@@ -127,6 +129,14 @@ class NttPlan:
 
     def set_chunk(self, limb_polys: int) -> None:
         check(lib().mfhe_ntt_plan_set_chunk(self._h, limb_polys))
+
+    @property
+    def arith(self) -> int:
+        """0: integer butterflies; 1: FP64-pipe butterflies (flat plans with every modulus below 2^50, then the default)."""
+        return lib().mfhe_ntt_plan_arith(self._h)
+
+    def set_arith(self, arith: int) -> None:
+        check(lib().mfhe_ntt_plan_set_arith(self._h, arith))
 
     def _batch(self, t, limbs=None) -> int:
         per = (limbs or self.limbs) * self.n

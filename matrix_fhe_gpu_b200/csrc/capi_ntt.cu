@@ -1,6 +1,7 @@
 // capi_ntt.cu -- C ABI (include/mfhe.h) for the NTT family: plans, transforms, pointwise ops.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -29,6 +30,7 @@ extern "C" void mfhe_ntt_plan_destroy(mfhe_ntt_plan* p) {
     if (!p) return;
     cudaFree(p->d_moduli); cudaFree(p->d_tw); cudaFree(p->d_itw);
     cudaFree(p->d_ninv); cudaFree(p->d_w1n); cudaFree(p->d_stage); cudaFree(p->d_mu);
+    cudaFree(p->d_twd); cudaFree(p->d_itwd); cudaFree(p->d_ninvd); cudaFree(p->d_w1nd);
     for (cudaStream_t st : p->host_streams) if (st) cudaStreamDestroy(st);
     delete p;
 }
@@ -87,7 +89,34 @@ extern "C" int mfhe_ntt_plan_create(int logn, int L, const uint64_t* moduli, int
     UP(p->d_w1n, w1n.data(), L * sizeof(tw_t));
     UP(p->d_mu, mu.data(), L * sizeof(ulonglong2));
 #undef UP
+    // every modulus below 2^50: the transforms can run on the FP64 pipe (modmath.cuh); on by default, MFHE_NTT_ARITH=int
+    // keeps the integer kernels, mfhe_ntt_plan_set_arith switches a plan
+    uint64_t qmax = 0;
+    for (int l = 0; l < L; ++l) qmax = std::max(qmax, moduli[l]);
+    if ((flat || convention == MFHE_NTT_PHANTOM_NEGACYCLIC) && qmax < (1ull << 50)) {
+        if ((e = cudaMalloc((void**)&p->d_twd, n * L * sizeof(tw_t))) != cudaSuccess ||
+            (e = cudaMalloc((void**)&p->d_itwd, n * L * sizeof(tw_t))) != cudaSuccess ||
+            (e = cudaMalloc((void**)&p->d_ninvd, L * sizeof(tw_t))) != cudaSuccess ||
+            (e = cudaMalloc((void**)&p->d_w1nd, L * sizeof(tw_t))) != cudaSuccess ||
+            (e = mfhe::ntt_fp_tables_launch(p->d_tw, p->d_twd, p->d_moduli, n, L, nullptr)) != cudaSuccess ||
+            (e = mfhe::ntt_fp_tables_launch(p->d_itw, p->d_itwd, p->d_moduli, n, L, nullptr)) != cudaSuccess ||
+            (e = mfhe::ntt_fp_tables_launch(p->d_ninv, p->d_ninvd, p->d_moduli, 1, L, nullptr)) != cudaSuccess ||
+            (e = mfhe::ntt_fp_tables_launch(p->d_w1n, p->d_w1nd, p->d_moduli, 1, L, nullptr)) != cudaSuccess ||
+            (e = cudaDeviceSynchronize()) != cudaSuccess) {
+            mfhe_ntt_plan_destroy(p); return cuda_fail(e, "plan_create fp64 tables");
+        }
+        const char* env = getenv("MFHE_NTT_ARITH");
+        p->arith = (env && !strcmp(env, "int")) ? 0 : 1;
+    }
     *out = p;
+    return MFHE_OK;
+}
+
+extern "C" int mfhe_ntt_plan_arith(const mfhe_ntt_plan* p) { return p ? p->arith : MFHE_EINVAL; }
+extern "C" int mfhe_ntt_plan_set_arith(mfhe_ntt_plan* p, int arith) {
+    if (!p || (arith != 0 && arith != 1)) return fail(MFHE_EINVAL, "set_arith: 0 (integer) or 1 (FP64 pipe)");
+    if (arith && !p->d_twd) return fail(MFHE_EUNSUPPORTED, "set_arith: the FP64-pipe arithmetic needs every modulus below 2^50 (and the Phantom negacyclic convention for n <= 256)");
+    p->arith = arith;
     return MFHE_OK;
 }
 

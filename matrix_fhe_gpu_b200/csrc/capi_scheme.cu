@@ -558,7 +558,7 @@ static int encrypt_core(mfhe_ctx* c, const uint64_t* m_re, const uint64_t* m_im,
         r.m0 = (const u64*)m_re; r.e0 = E0; r.o0 = (u64*)ct_re;
         if (ct_im) { r.m1 = (const u64*)m_im; r.e1 = E1; r.o1 = (u64*)ct_im; }
         r.subtract = 1; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
-        e = xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+        e = xrow_mul_s_launch(r, c->xy_plan->small_rows(), c->d_mu, st);
     }
     return done(e, who);
 }
@@ -617,7 +617,7 @@ extern "C" int mfhe_encode_encrypt_pair(mfhe_ctx* c, const double* msg, const ui
         r.m0 = (const u64*)ct_re; r.o0 = (u64*)ct_re;
         r.m1 = (const u64*)ct_im; r.o1 = (u64*)ct_im;
         r.subtract = 1; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
-        e = xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+        e = xrow_mul_s_launch(r, c->xy_plan->small_rows(), c->d_mu, st);
     }
     return done(e, "encode_encrypt_pair");
 }
@@ -629,7 +629,7 @@ static cudaError_t decrypt_rows(mfhe_ctx* c, const u64* ct, const u64* sk, u64* 
     RowArgs r;
     r.a = ct + c->T(); r.s = sk; r.m0 = ct; r.o0 = out; r.o_layout = out_layout;
     r.subtract = 0; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
-    return xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+    return xrow_mul_s_launch(r, c->xy_plan->small_rows(), c->d_mu, st);
 }
 extern "C" int mfhe_decrypt_to_eval(mfhe_ctx* c, const uint64_t* ct, const uint64_t* sk, uint64_t* out, int layout, void* s) {
     if (!c || !ct || !sk || !out || (layout & ~1)) return fail(MFHE_EINVAL, "decrypt_to_eval: bad argument");
@@ -647,7 +647,7 @@ extern "C" int mfhe_decrypt_decode(mfhe_ctx* c, const uint64_t* ct_re, const uin
     r.a = (const u64*)ct_re + c->T(); r.a1 = (const u64*)ct_im + c->T(); r.s = (const u64*)sk;
     r.m0 = (const u64*)ct_re; r.o0 = mr; r.m1 = (const u64*)ct_im; r.o1 = mi;
     r.o_layout = MFHE_LAYOUT_MATRIX; r.subtract = 0; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
-    cudaError_t e = xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, S(s));
+    cudaError_t e = xrow_mul_s_launch(r, c->xy_plan->small_rows(), c->d_mu, S(s));
     if (e == cudaSuccess) e = decode_tail(c, mr, mi, MFHE_LAYOUT_MATRIX, (double2*)out, S(s));
     if (e == cudaErrorMemoryAllocation) return fail(MFHE_ENOMEM, "decrypt_decode: arena too small");
     return done(e, "decrypt_decode");
@@ -745,7 +745,7 @@ extern "C" int mfhe_ct_matmul_decrypt(mfhe_ctx* c, uint64_t* prod, const uint64_
         RowArgs r;                                      // (o_r, o_i) = (mr, mi) + (ar, ai) (*) s along the fast index
         r.a = ar; r.a1 = ai; r.s = (const u64*)sk; r.m0 = mr; r.o0 = o_r; r.m1 = mi; r.o1 = o_i;
         r.subtract = 0; r.n = c->n; r.limbs = c->L; r.phi = c->phi;
-        return xrow_mul_s_launch(r, c->xy_plan->small(), c->d_mu, st);
+        return xrow_mul_s_launch(r, c->xy_plan->small_rows(), c->d_mu, st);
     };
     const size_t mats = (size_t)c->phi * c->L;
     // 1. D_bb += D_ba (*)_z s      2. D_ab += D_aa (*)_z s      (in place)

@@ -194,6 +194,8 @@ __host__ __device__ constexpr int fwd_bound_before(int s, int logn) {
 // subtracts canonicalise the outputs.
 struct qconst_t { u64 q, q2, q4, nq, cneg; };
 __device__ __forceinline__ qconst_t make_qconst(u64 q) { return qconst_t{q, 2 * q, 4 * q, 0 - q, fpq_cneg(q)}; }
+// per-arithmetic constants of a limb: AR = 0 the integer forms above, AR = 1 the FP64-pipe forms below (q < 2^50)
+template <int AR> struct arith_const;
 
 template <int LOGN, int S>
 __device__ __forceinline__ void ct_bfly(u64& x, u64& y, const twf_t& w, tw_t raw, const qconst_t& c) {
@@ -218,6 +220,110 @@ __device__ __forceinline__ void gs_bfly(u64& x, u64& y, const twf_t& w, const qc
     x = csub(x + y, c.q4);
     y = mul_fpq(t, w, c.nq, c.cneg);
 }
+
+// ---- FP64-pipe arithmetic for moduli below 2^50 -------------------------------------------------------------------
+// The fmaheavy pipe binds the 64-bit butterflies above (a modular product is 3 IMAD.WIDE + 2 IMAD.HI + 4 IMAD); the FP64
+// pipe of B200 issues DFMA at the IMAD rate and a DFMA multiplies 53-bit mantissas.  For q < 2^50 the whole butterfly
+// fits there (profiles/microbench/fp64bfly.cu: 14.0 G butterflies/s/SM against 6.5 for the integer form):
+//   * a value is an integer-valued double, |v| <= B q with B tracked at compile time (units of q/16 below);
+//   * a twiddle is {w, w/q} with w centred in (-q/2, q/2) -- 16 bytes, same table shape as {w, w'};
+//   * t = y w - rint(y w / q) q EXACTLY: h = y*w, l = fma(y, w, -h) (error-free product), k = rint(y * (w/q)) through the
+//     1.5 * 2^52 trick, d = fma(-k, q, h) (exact: an integer below 2^53), t = d + l (exact).  6 FP64-pipe operations.
+//     |k - y w / q| <= 1/2 + |y w / q| 2^-53, |y w / q| <= B q / 2 < B 2^49, hence |t| <= q (1/2 + B/16); the rounding
+//     trick needs |y (w/q)| <= 2^51, i.e. B <= 4.  (Exhaustive-style CPU check of exactly these expressions -- IEEE fma
+//     is bit-identical on both machines -- in tests/test_fp64_modmul.py.)
+//   * folding a value back to |v| <= q/2 (+ rounding slack) is fma / add / fma.
+// Results leave through fp_store as canonical residues, so the two arithmetics are interchangeable word for word.
+struct fconst_t { double q, qinv; u64 qi; };
+constexpr double kRint = 6755399441055744.0;                 // 1.5 * 2^52
+__device__ __forceinline__ fconst_t make_fconst(u64 q) {
+    const double qd = (double)(long long)q;
+    return fconst_t{qd, __ddiv_rn(1.0, qd), q};
+}
+__device__ __forceinline__ double d_of(u64 v) { return __longlong_as_double((long long)v); }
+__device__ __forceinline__ u64 u_of(double d) { return (u64)__double_as_longlong(d); }
+__device__ __forceinline__ double fp_mul(double y, double w, double wq, const fconst_t& c) {
+    const double h = __dmul_rn(y, w), l = __fma_rn(y, w, -h);
+    const double k = __dadd_rn(__fma_rn(y, wq, kRint), -kRint);
+    return __dadd_rn(__fma_rn(-k, c.q, h), l);
+}
+__device__ __forceinline__ double fp_fold(double x, const fconst_t& c) {
+    const double k = __dadd_rn(__fma_rn(x, c.qinv, kRint), -kRint);
+    return __fma_rn(-k, c.q, x);
+}
+// residue below 2^52 -> double (the pattern {x, 0x43300000} is 2^52 + x)
+__device__ __forceinline__ double fp_load(u64 x) { return __dadd_rn(d_of(x | 0x4330000000000000ull), -4503599627370496.0); }
+// integer-valued |r| < q -> canonical residue: through the integer pattern of r + 1.5 * 2^52 (so -0.0 is 0)
+__device__ __forceinline__ u64 fp_store(double r, const fconst_t& c) {
+    const long long i = __double_as_longlong(__dadd_rn(r, kRint)) - 0x4338000000000000ll;
+    return (u64)(i + ((i >> 63) & (long long)c.qi));
+}
+
+// bounds in units of q/16
+constexpr int kFpLim = 64;                                   // a multiplied value must stay within 4q
+constexpr int kFpFolded = 9;                                 // after fp_fold: q/2 + rounding slack
+constexpr int kFpIn = 32;                                    // transform inputs may be in [0, 2q)
+__host__ __device__ constexpr int fp_t(int B) { return 8 + (B + 15) / 16; }           // |y w mod q| for |y| <= B
+__host__ __device__ constexpr bool fp_fwd_fold(int B) { return B + fp_t(B) > kFpLim; }
+__host__ __device__ constexpr int fp_fwd_bound_before(int s) {
+    int B = kFpIn;
+    for (int i = 0; i < s; ++i) B = (fp_fwd_fold(B) ? kFpFolded : B) + fp_t(B);
+    return B;
+}
+// inverse network: both outputs of a stage enter the next one as either operand
+__host__ __device__ constexpr bool fp_inv_fold(int B) { return 2 * B > kFpLim / 2; }
+__host__ __device__ constexpr int fp_inv_bound_before(int i) {
+    int B = kFpIn;
+    for (int j = 0; j < i; ++j) {
+        const int xb = fp_inv_fold(B) ? kFpFolded : 2 * B, yb = fp_t(2 * B);
+        B = xb > yb ? xb : yb;
+    }
+    return B;
+}
+
+// bound of the values a forward network of 2^logn points leaves when its final fold is skipped
+__host__ __device__ constexpr int fp_fwd_out_bound(int logn) { return fp_fwd_bound_before(logn - 1) + fp_t(fp_fwd_bound_before(logn - 1)); }
+// product with a NON-constant multiplicand s in [0, q) (no precomputed s/q): the quotient comes from h * (1/q), two
+// roundings instead of one, |k - y s / q| <= 1/2 + |y s / q| 2^-52.  Needs |y| <= q (callers fold first); |t| < q.
+__device__ __forceinline__ double fp_mul_generic(double y, double s, const fconst_t& c) {
+    const double h = __dmul_rn(y, s), l = __fma_rn(y, s, -h);
+    const double k = __dadd_rn(__fma_rn(h, c.qinv, kRint), -kRint);
+    return __dadd_rn(__fma_rn(-k, c.q, h), l);
+}
+
+// Cooley-Tukey butterfly at global stage S on doubles; x, y carry the bit patterns
+template <int LOGN, int S>
+__device__ __forceinline__ void ct_bfly_fp(u64& x, u64& y, tw_t w, const fconst_t& c) {
+    constexpr int B = fp_fwd_bound_before(S);
+    static_assert(B <= kFpLim, "forward bound schedule");
+    double X = d_of(x);
+    if constexpr (fp_fwd_fold(B) && S != LOGN - 1) X = fp_fold(X, c);          // the last stage is folded on the way out
+    const double t = fp_mul(d_of(y), d_of(w.x), d_of(w.y), c);
+    y = u_of(__dadd_rn(X, -t));
+    x = u_of(__dadd_rn(X, t));
+}
+// Gentleman-Sande butterfly at inverse stage I (global bit I)
+template <int LOGN, int I>
+__device__ __forceinline__ void gs_bfly_fp(u64& x, u64& y, tw_t w, const fconst_t& c) {
+    constexpr int B = fp_inv_bound_before(I);
+    static_assert(2 * B <= kFpLim, "inverse bound schedule");
+    const double X = d_of(x), Y = d_of(y);
+    double sum = __dadd_rn(X, Y);
+    if constexpr (fp_inv_fold(B)) sum = fp_fold(sum, c);
+    x = u_of(sum);
+    y = u_of(fp_mul(__dadd_rn(X, -Y), d_of(w.x), d_of(w.y), c));
+}
+// last inverse stage: both outputs multiplied (n^-1 and w * n^-1), canonical residues out
+template <int LOGN>
+__device__ __forceinline__ void gs_last_fp(u64& x, u64& y, tw_t ninv, tw_t w1n, const fconst_t& c) {
+    static_assert(2 * fp_inv_bound_before(LOGN - 1) <= kFpLim, "inverse bound schedule");
+    const double X = d_of(x), Y = d_of(y);
+    x = fp_store(fp_mul(__dadd_rn(X, Y), d_of(ninv.x), d_of(ninv.y), c), c);
+    y = fp_store(fp_mul(__dadd_rn(X, -Y), d_of(w1n.x), d_of(w1n.y), c), c);
+}
+
+template <> struct arith_const<0> { typedef qconst_t type; static __device__ __forceinline__ type make(u64 q) { return make_qconst(q); } };
+template <> struct arith_const<1> { typedef fconst_t type; static __device__ __forceinline__ type make(u64 q) { return make_fconst(q); } };
 
 // generic (non-constant multiplicand) product, Barrett on the 128-bit product.
 // mu = floor(2^128 / q) as {lo, hi}; result canonical.

@@ -12,6 +12,9 @@ cudaError_t ntt_flat_launch(bool forward, u64* data, const NttTables& T, int lim
                             int limb_count, size_t batch, size_t chunk_limb_polys,
                             cudaStream_t st, const u64* mul = nullptr, const ulonglong2* mu = nullptr);
 
+// twiddle tables of the FP64-pipe arithmetic from the integer ones ({w, w'} -> {centred w, w / q} as doubles)
+cudaError_t ntt_fp_tables_launch(const tw_t* src, tw_t* dst, const u64* moduli, size_t per, int L, cudaStream_t st);
+
 // small transforms, n = 2^3..2^8, one warp-slice per limb-poly (ntt_small.cu)
 enum SmallConvention { kPhantomNegacyclic = 0, kGlXnMinusI = 1, kCyclicNatural = 2 };
 struct SmallTables {
@@ -25,6 +28,7 @@ struct SmallTables {
     int logn;
     int L;
     int convention;
+    int arith;            // 1: tw / itw / ninv / w1n are the FP64-pipe tables {w, w/q} (fused row kernel of scheme.cu only)
 };
 cudaError_t ntt_small_launch(bool forward, u64* data, const SmallTables& T, int limbs,
                              size_t batch, cudaStream_t st);

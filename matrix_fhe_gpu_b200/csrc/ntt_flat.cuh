@@ -33,6 +33,7 @@ struct NttTables {            // device pointers, per plan
     const tw_t* w1n;          // [L]    {itw[1] * n^-1, shoup}: last inverse stage
     int logn;
     int L;
+    int arith;                // 0: integer arithmetic, tw = {w, w'};  1: FP64-pipe arithmetic (q < 2^50), tw = {w, w/q} as doubles
 };
 
 // ---------------------------------------------------------------------------
@@ -47,9 +48,15 @@ struct NttTables {            // device pointers, per plan
 //   g0    global coefficient index of v[.][0]
 // Stage for global bit b: s = LOGN-1-b, twiddle index 2^s + (g >> (b+1)).
 // ---------------------------------------------------------------------------
-template <int LOGN, int GB, int ACT, int PB>
+template <class QC> struct is_fp_arith { static constexpr bool value = false; };
+template <> struct is_fp_arith<fconst_t> { static constexpr bool value = true; };
+
+// QC = qconst_t: integer arithmetic (any q < 2^60); QC = fconst_t: FP64-pipe arithmetic (q < 2^50, tables of {w, w/q},
+// v holds the bit patterns of doubles) -- same index structure, same twiddle fetches
+template <int LOGN, int GB, int ACT, int PB, class QC>
 __device__ __forceinline__ void fwd_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __restrict__ tw,
-                                         const qconst_t& c) {
+                                         const QC& c) {
+    constexpr bool FP = is_fp_arith<QC>::value;
 #pragma unroll
     for (int tb = 2; tb >= 0; --tb) {
         if (!((ACT >> tb) & 1)) continue;
@@ -59,6 +66,18 @@ __device__ __forceinline__ void fwd_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
 #pragma unroll
         for (int jh = 0; jh < (4 >> tb); ++jh) {
             const tw_t raw = __ldg(tw + base + jh);
+            if constexpr (FP) {
+#pragma unroll
+                for (int p = 0; p < PB; ++p) {
+#pragma unroll
+                    for (int jl = 0; jl < (1 << tb); ++jl) {
+                        const int jx = (jh << (tb + 1)) | jl;
+                        if (tb == 2) ct_bfly_fp<LOGN, LOGN - 1 - (GB + 2)>(v[p][jx], v[p][jx | 4], raw, c);
+                        if (tb == 1) ct_bfly_fp<LOGN, LOGN - 1 - (GB + 1)>(v[p][jx], v[p][jx | 2], raw, c);
+                        if (tb == 0) ct_bfly_fp<LOGN, LOGN - 1 - (GB + 0)>(v[p][jx], v[p][jx | 1], raw, c);
+                    }
+                }
+            } else {
             twf_t w;
             if (s != LOGN - 1) w = fpq_prep(raw);
 #pragma unroll
@@ -72,13 +91,15 @@ __device__ __forceinline__ void fwd_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
                     if (tb == 0) ct_bfly<LOGN, LOGN - 1 - (GB + 0)>(v[p][jx], v[p][jx | 1], w, raw, c);
                 }
             }
+            }
         }
     }
 }
 
-template <int LOGN, int GB, int ACT, int PB>
+template <int LOGN, int GB, int ACT, int PB, class QC>
 __device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __restrict__ itw,
-                                         const qconst_t& c, tw_t ninv, tw_t w1n) {
+                                         const QC& c, tw_t ninv, tw_t w1n) {
+    constexpr bool FP = is_fp_arith<QC>::value;
 #pragma unroll
     for (int tb = 0; tb <= 2; ++tb) {
         if (!((ACT >> tb) & 1)) continue;
@@ -87,6 +108,22 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
         const u32 base = (1u << s) + (g0 >> (b + 1));
 #pragma unroll
         for (int jh = 0; jh < (4 >> tb); ++jh) {
+            if constexpr (FP) {
+                tw_t raw = {0, 0};
+                if (b != LOGN - 1) raw = __ldg(itw + base + jh);
+#pragma unroll
+                for (int p = 0; p < PB; ++p) {
+#pragma unroll
+                    for (int jl = 0; jl < (1 << tb); ++jl) {
+                        const int jx = (jh << (tb + 1)) | jl;
+                        const int jy = jx | (1 << tb);
+                        if (b == LOGN - 1) gs_last_fp<LOGN>(v[p][jx], v[p][jy], ninv, w1n, c);
+                        else if (tb == 0) gs_bfly_fp<LOGN, GB + 0>(v[p][jx], v[p][jy], raw, c);
+                        else if (tb == 1) gs_bfly_fp<LOGN, GB + 1>(v[p][jx], v[p][jy], raw, c);
+                        else              gs_bfly_fp<LOGN, GB + 2>(v[p][jx], v[p][jy], raw, c);
+                    }
+                }
+            } else {
             twf_t w;
             if (b != LOGN - 1) w = fpq_prep(__ldg(itw + base + jh));
 #pragma unroll
@@ -107,6 +144,7 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
                     }
                 }
             }
+            }
         }
     }
 }
@@ -115,13 +153,13 @@ __device__ __forceinline__ void inv_pass(u64 (&v)[PB][8], u32 g0, const tw_t* __
 template <int LOGN, int GB, int ACT>
 __device__ __forceinline__ void fwd_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ tw, u64 q, u64 /*q2*/) {
     const qconst_t c = make_qconst(q);
-    fwd_pass<LOGN, GB, ACT, 1>(reinterpret_cast<u64 (&)[1][8]>(v), g0, tw, c);
+    fwd_pass<LOGN, GB, ACT, 1, qconst_t>(reinterpret_cast<u64 (&)[1][8]>(v), g0, tw, c);
 }
 template <int LOGN, int GB, int ACT>
 __device__ __forceinline__ void inv_pass(u64 (&v)[8], u32 g0, const tw_t* __restrict__ itw, u64 q, u64 /*q2*/,
                                          tw_t ninv, tw_t w1n) {
     const qconst_t c = make_qconst(q);
-    inv_pass<LOGN, GB, ACT, 1>(reinterpret_cast<u64 (&)[1][8]>(v), g0, itw, c, ninv, w1n);
+    inv_pass<LOGN, GB, ACT, 1, qconst_t>(reinterpret_cast<u64 (&)[1][8]>(v), g0, itw, c, ninv, w1n);
 }
 
 // position of element j of a thread whose remaining index bits are u, triple at P

@@ -51,6 +51,67 @@ struct SmallNet {
         for (int j = 0; j < 8; ++j) { v[j] = csub(v[j], q2); v[j] = csub(v[j], q); }
     }
 
+    // FP64-pipe forms (q < 2^50, tables of {w, w/q}; modmath.cuh).  forward_fp leaves integer-valued doubles (bit patterns)
+    // with |v| <= fp_fwd_out_bound(LOGN) q/16 at the same positions; inverse_fp takes doubles with |v| <= 2q and returns
+    // canonical residues exactly like inverse().
+    __device__ static __forceinline__ void forward_fp(u64 (&v)[8], const u64* __restrict__ g, u64* sm, u32 u,
+                                                      const tw_t* __restrict__ tw, const fconst_t& c) {
+        u64 (&V)[1][8] = reinterpret_cast<u64 (&)[1][8]>(v);
+        {
+            const u32 e0 = deposit3(u, FP0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = u_of(fp_load(g[e0 + (j << FP0)]));
+            fwd_pass<LOGN, FP0, 7, 1, fconst_t>(V, e0, tw, c);
+            if constexpr (FP0 > 0) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sm[swz(e0 + (j << FP0))] = v[j];
+            }
+        }
+        if constexpr (FP0 > 0) {
+            __syncwarp();
+            const u32 e1 = deposit3(u, FP1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << FP1))];
+            fwd_pass<LOGN, FP1, (1 << (FP0 - FP1)) - 1, 1, fconst_t>(V, e1, tw, c);
+            if constexpr (FP1 > 0) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << FP1))] = v[j];
+                __syncwarp();
+                const u32 e2 = deposit3(u, FP2);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << FP2))];
+                fwd_pass<LOGN, FP2, (1 << (FP1 - FP2)) - 1, 1, fconst_t>(V, e2, tw, c);
+            }
+        }
+    }
+    __device__ static __forceinline__ u32 inverse_fp(u64 (&v)[8], u64* sm, u32 u, const tw_t* __restrict__ itw,
+                                                     const fconst_t& c, tw_t ninv, tw_t w1n) {
+        u64 (&V)[1][8] = reinterpret_cast<u64 (&)[1][8]>(v);
+        inv_pass<LOGN, 0, 7, 1, fconst_t>(V, 8 * u, itw, c, ninv, w1n);
+        if constexpr (PL > 0) {
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[swz(8 * u + j)] = v[j];
+            __syncwarp();
+            const u32 e1 = deposit3(u, IP1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = sm[swz(e1 + (j << IP1))];
+            inv_pass<LOGN, IP1, 7 & ~((1 << (3 - IP1)) - 1), 1, fconst_t>(V, e1, itw, c, ninv, w1n);
+            if constexpr (PL > 3) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sm[swz(e1 + (j << IP1))] = v[j];
+                __syncwarp();
+                const u32 e2 = deposit3(u, IP2);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = sm[swz(e2 + (j << IP2))];
+                inv_pass<LOGN, IP2, 7 & ~((1 << (IP1 + 3 - IP2)) - 1), 1, fconst_t>(V, e2, itw, c, ninv, w1n);
+                return e2;
+            }
+            return e1;
+        }
+        return 8 * u;
+    }
+
     // the value inverse() returns, known before the transform (lets the caller prefetch what it combines with)
     __device__ static __forceinline__ u32 out_base(u32 u) {
         if constexpr (PL > 3) return deposit3(u, IP2);

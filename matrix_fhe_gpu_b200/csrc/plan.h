@@ -12,15 +12,27 @@ struct mfhe_ntt_plan {
     std::vector<uint64_t> moduli, roots;
     u64* d_moduli = nullptr;
     tw_t *d_tw = nullptr, *d_itw = nullptr, *d_ninv = nullptr, *d_w1n = nullptr;
+    // FP64-pipe arithmetic (flat plans whose moduli are all below 2^50): {centred w, w / q} as doubles, same shapes
+    tw_t *d_twd = nullptr, *d_itwd = nullptr, *d_ninvd = nullptr, *d_w1nd = nullptr;
+    int arith = 0;                             // 0 integer, 1 FP64 pipe (mfhe_ntt_plan_set_arith)
     ulonglong2* d_mu = nullptr;                // [L] floor(2^128 / q) as {lo, hi} (Barrett)
     std::vector<mfhe::host::TwPair> h_tw, h_itw;     // kept for mfhe_ntt_plan_get_table
     size_t chunk = 0;
     uint64_t* d_stage = nullptr;               // staging for the *_host entry points
     size_t stage_bytes = 0;
     cudaStream_t host_streams[3] = {nullptr, nullptr, nullptr};   // H2D / compute / D2H of the *_host entry points (lazy)
-    NttTables flat() const { return NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L}; }
+    NttTables flat() const {
+        return arith ? NttTables{d_moduli, d_twd, d_itwd, d_ninvd, d_w1nd, logn, L, 1}
+                     : NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L, 0};
+    }
     SmallTables small() const {
-        return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention};
+        return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention, 0};
+    }
+    // the fused encrypt / decrypt row kernel (scheme.cu) can run its transforms on the FP64 pipe
+    SmallTables small_rows() const {
+        if (arith && convention == MFHE_NTT_PHANTOM_NEGACYCLIC)
+            return SmallTables{d_moduli, d_twd, d_itwd, d_ninvd, d_w1nd, nullptr, nullptr, logn, L, convention, 1};
+        return small();
     }
 };
 

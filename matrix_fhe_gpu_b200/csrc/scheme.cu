@@ -24,7 +24,9 @@ __device__ __forceinline__ size_t row_offset(int layout, u32 w, u32 l, u32 y, in
 #ifndef MFHE_XROW_MINB
 #define MFHE_XROW_MINB 4
 #endif
-template <int LOGN, bool DUAL>
+// AR = 1: the two transforms and the key product run on the FP64 pipe (every modulus below 2^50, T carries the
+// {w, w/q} tables; modmath.cuh) -- same words out, the reference's 45- and 35-bit moduli qualify
+template <int LOGN, bool DUAL, int AR>
 __global__ void __launch_bounds__(256, MFHE_XROW_MINB)
 xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_tab, size_t rows) {
     using Net = SmallNet<LOGN>;
@@ -52,6 +54,18 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
     const int passes = (DUAL && !shared_t) ? 2 : 1;       // DUAL = false: one pass, compile-time
     for (int pass = 0; pass < passes; ++pass) {
     u64 v[8];
+    u32 e;
+    if constexpr (AR) {
+        const fconst_t fc = make_fconst(q);
+        Net::forward_fp(v, ((DUAL && pass) ? r.a1 : r.a) + ao, sm, u, T.tw + ((size_t)l << LOGN), fc);
+        const u64* s = r.s + ((size_t)wl << LOGN) + 8 * u;
+        const ulonglong2 s0 = __ldg((const ulonglong2*)s), s1 = __ldg((const ulonglong2*)s + 1),
+                         s2 = __ldg((const ulonglong2*)s + 2), s3 = __ldg((const ulonglong2*)s + 3);
+        const u64 sv[8] = {s0.x, s0.y, s1.x, s1.y, s2.x, s2.y, s3.x, s3.y};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = u_of(fp_mul_generic(fp_fold(d_of(v[j]), fc), fp_load(sv[j]), fc));
+        e = Net::inverse_fp(v, sm, u, T.itw + ((size_t)l << LOGN), fc, T.ninv[l], T.w1n[l]);
+    } else {
     Net::forward(v, ((DUAL && pass) ? r.a1 : r.a) + ao, sm, u, T.tw + ((size_t)l << LOGN), q, q2);
     {
         const u64* s = r.s + ((size_t)wl << LOGN) + 8 * u;      // key is stored in the same bit-reversed order
@@ -63,7 +77,8 @@ xrow_mul_s_kernel(RowArgs r, SmallTables T, const ulonglong2* __restrict__ mu_ta
         v[4] = mul_barrett1(v[4], s2.x, bc); v[5] = mul_barrett1(v[5], s2.y, bc);
         v[6] = mul_barrett1(v[6], s3.x, bc); v[7] = mul_barrett1(v[7], s3.y, bc);
     }
-    const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)l << LOGN), q, q2, T.ninv[l], T.w1n[l]);
+    e = Net::inverse(v, sm, u, T.itw + ((size_t)l << LOGN), q, q2, T.ninv[l], T.w1n[l]);
+    }
 #pragma unroll
     for (int comp = 0; comp < 2; ++comp) {
         if (passes == 2 && comp != pass) continue;
@@ -91,8 +106,14 @@ cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulon
 #define MFHE_ROW_CASE(LN)                                                                       \
     case LN: {                                                                                  \
         constexpr int PPB = 256 / ((1 << LN) / 8);                                              \
-        if (r.a1 && r.o1) xrow_mul_s_kernel<LN, true><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
-        else xrow_mul_s_kernel<LN, false><<<(unsigned)((rows + PPB - 1) / PPB), 256, 0, st>>>(r, T, mu, rows); \
+        const unsigned grid = (unsigned)((rows + PPB - 1) / PPB);                               \
+        if (T.arith) {                                                                          \
+            if (r.a1 && r.o1) xrow_mul_s_kernel<LN, true, 1><<<grid, 256, 0, st>>>(r, T, mu, rows); \
+            else xrow_mul_s_kernel<LN, false, 1><<<grid, 256, 0, st>>>(r, T, mu, rows);         \
+        } else {                                                                                \
+            if (r.a1 && r.o1) xrow_mul_s_kernel<LN, true, 0><<<grid, 256, 0, st>>>(r, T, mu, rows); \
+            else xrow_mul_s_kernel<LN, false, 0><<<grid, 256, 0, st>>>(r, T, mu, rows);         \
+        }                                                                                       \
         break; }
     switch (T.logn) {
         MFHE_ROW_CASE(4) MFHE_ROW_CASE(5) MFHE_ROW_CASE(6) MFHE_ROW_CASE(7) MFHE_ROW_CASE(8)

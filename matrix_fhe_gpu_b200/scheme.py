@@ -137,6 +137,20 @@ class Context:
         import torch
         return torch.empty(numel, dtype=dtype or torch.int64, device=like.device if like is not None else "cuda")
 
+    def set_row_arith(self, arith: int) -> None:
+        """Arithmetic of the fused encrypt / decrypt row kernel (X transforms + key product): 0 integer, 1 FP64 pipe
+        (the default when every modulus is below 2^50).  Same words either way; for A/B runs and parity tests."""
+        import ctypes as C
+        L = lib()
+        L.mfhe_ntt_plan_set_arith.argtypes = [_vp, C.c_int]
+        check(L.mfhe_ntt_plan_set_arith(L.mfhe_ctx_xy_plan(self._h), arith))
+
+    @property
+    def row_arith(self) -> int:
+        L = lib()
+        L.mfhe_ntt_plan_arith.argtypes = [_vp]
+        return L.mfhe_ntt_plan_arith(L.mfhe_ctx_xy_plan(self._h))
+
     def eta(self, limb):
         return int(_L().mfhe_ctx_eta(self._h, limb))
 

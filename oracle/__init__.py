@@ -83,6 +83,13 @@ def lib() -> C.CDLL:
             getattr(L, name).restype = None
             getattr(L, name).argtypes = [_p64, C.c_int, u64]
         L.mfo_gl_perm.restype = None; L.mfo_gl_perm.argtypes = [C.c_int, _p32, _p32]
+        _pd = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+        L.mfo_fp64_modmul_check.restype = C.c_long
+        L.mfo_fp64_modmul_check.argtypes = [u64, C.c_long, u64, C.c_int, C.POINTER(C.c_double)]
+        L.mfo_fp64_negacyclic_forward.restype = C.c_int
+        L.mfo_fp64_negacyclic_forward.argtypes = [_p64, C.c_int, u64, _p64, _pd]
+        L.mfo_fp64_negacyclic_inverse.restype = C.c_int
+        L.mfo_fp64_negacyclic_inverse.argtypes = [_p64, C.c_int, u64, _p64, u64, _pd]
         _lib = L
     return _lib
 
@@ -194,6 +201,26 @@ class PhantomTables:
                                            self.itw.reshape(-1), self.itws.reshape(-1),
                                            self.n_inv, self.n_inv_shoup)
         return d
+
+
+def fp64_modmul_check(q: int, count: int, seed: int, bound16: int):
+    """(failures, max |t| / q) of the FP64-pipe modular product over `count` operand pairs with |y| <= bound16/16 * q."""
+    mx = C.c_double()
+    bad = lib().mfo_fp64_modmul_check(int(q), count, seed, bound16, C.byref(mx))
+    return int(bad), float(mx.value)
+
+
+def fp64_ntt(poly: np.ndarray, logn: int, q: int, table: np.ndarray, inverse: bool = False, n_inv: int = 0):
+    """One limb-poly through the FP64-pipe arithmetic of the CUDA kernels, emulated on the CPU with the kernels' fold
+    schedule.  Returns (result, rc, largest |v| / q entering every stage); rc < 0 names a stage that broke its bound."""
+    a = np.ascontiguousarray(poly, dtype=np.uint64).copy()
+    st = np.zeros(logn, dtype=np.float64)
+    tab = np.ascontiguousarray(table, dtype=np.uint64)
+    if inverse:
+        rc = lib().mfo_fp64_negacyclic_inverse(a, logn, int(q), tab, int(n_inv), st)
+    else:
+        rc = lib().mfo_fp64_negacyclic_forward(a, logn, int(q), tab, st)
+    return a, int(rc), st
 
 
 def splitmix64(x: np.ndarray) -> np.ndarray:

@@ -69,6 +69,12 @@ void mfo_negacyclic_forward_def(const uint64_t *a, uint64_t *out, int logn,
 void mfo_schoolbook_mul(const uint64_t *a, const uint64_t *b, uint64_t *c,
                         size_t n, uint64_t q, uint64_t wrap);
 
+/* FP64-pipe arithmetic of the CUDA kernels for q < 2^50 (csrc/modmath.cuh), same expressions on the CPU: exactness
+ * of the modular product and the compile-time bound schedule of the two networks (ntt_oracle.c) */
+long mfo_fp64_modmul_check(uint64_t q, long count, uint64_t seed, int bound16, double *max_ratio);
+int mfo_fp64_negacyclic_forward(uint64_t *a, int logn, uint64_t q, const uint64_t *tw, double *stage_max);
+int mfo_fp64_negacyclic_inverse(uint64_t *a, int logn, uint64_t q, const uint64_t *itw, uint64_t n_inv, double *stage_max);
+
 /* flat RNS batch [batch][L][N], OpenMP over limb-polys: the timed CPU
  * baseline.  tables are [L][N] as produced by mfo_phantom_tables per limb.   */
 void mfo_negacyclic_forward_batch(uint64_t *data, size_t batch, size_t L, int logn,

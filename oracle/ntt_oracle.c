@@ -310,3 +310,121 @@ void mfo_gl_perm(int n, uint32_t *perm, uint32_t *inv_perm) {
         e = (uint32_t)((uint64_t)e * 5u % m);
     }
 }
+
+/* ---- FP64-pipe arithmetic of matrix_fhe_gpu_b200/csrc/modmath.cuh (q < 2^50), restated for the CPU ---------------
+ * IEEE-754 fma / add / mul are bit-identical on the host and on the GPU, so the exactness claims and the compile-time
+ * bound schedule of the kernels (fp_fwd_bound_before / fp_inv_bound_before) are checked here, without a GPU: the
+ * emulation below runs the same expressions in the same order of stages, records the largest |v| / q that enters
+ * every stage and fails when one exceeds the schedule.  Algorithm being replaced: the butterflies of
+ * ph/include/butterfly.cuh:10-37 (ct_butterfly / gs_butterfly) inside ph/src/ntt/ntt_1d.cu:17-76, 194-256. */
+#include <math.h>
+static const double kRint = 6755399441055744.0;           /* 1.5 * 2^52 */
+static double fp_mul(double y, double w, double wq, double q) {
+    double h = y * w, l = fma(y, w, -h);
+    double k = fma(y, wq, kRint) - kRint;
+    return fma(-k, q, h) + l;
+}
+static double fp_fold(double x, double q, double qinv) {
+    double k = fma(x, qinv, kRint) - kRint;
+    return fma(-k, q, x);
+}
+static int fp_t(int B) { return 8 + (B + 15) / 16; }
+static double centred(uint64_t w, uint64_t q) { return w > (q >> 1) ? (double)((int64_t)w - (int64_t)q) : (double)w; }
+static uint64_t fp_canon(double r, uint64_t q) { int64_t i = (int64_t)r; return (uint64_t)(i < 0 ? i + (int64_t)q : i); }
+
+/* products: count random (y, w) pairs with |y| <= bound16/16 * q plus the corner cases; returns the number of results
+ * that are not the exact integer y*w - k*q, *max_ratio = largest |t| / q seen */
+long mfo_fp64_modmul_check(uint64_t q, long count, uint64_t seed, int bound16, double *max_ratio) {
+    const double qd = (double)q;
+    const int64_t lim = (int64_t)((double)bound16 / 16.0 * qd);
+    long bad = 0; double mx = 0;
+    uint64_t s = seed * 0x9E3779B97F4A7C15ull + 1;
+    for (long it = 0; it < count; ++it) {
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17; uint64_t r1 = s;
+        s ^= s << 13; s ^= s >> 7; s ^= s << 17; uint64_t r2 = s;
+        int64_t w = (int64_t)(r1 % q); if (w > (int64_t)(q >> 1)) w -= (int64_t)q;
+        int64_t y = (int64_t)(r2 % (2 * (uint64_t)lim + 1)) - lim;
+        switch (it & 15) {
+            case 0: y = lim; break; case 1: y = -lim; break; case 2: w = (int64_t)(q >> 1); break;
+            case 3: w = -(int64_t)(q >> 1); break; case 4: y = lim; w = (int64_t)(q >> 1); break;
+            case 5: y = -lim; w = (int64_t)(q >> 1); break; case 6: y = 0; break; case 7: w = 0; break; default: break;
+        }
+        const double t = fp_mul((double)y, (double)w, (double)w / qd, qd);
+        if (t != (double)(int64_t)t) { ++bad; continue; }
+        __int128 d = (__int128)y * w - (__int128)(int64_t)t;
+        if (d % (__int128)q != 0) ++bad;
+        if (fabs(t) / qd > mx) mx = fabs(t) / qd;
+    }
+    if (max_ratio) *max_ratio = mx;
+    return bad;
+}
+
+/* whole transforms; tw / itw are Phantom-order integer tables (mfo_phantom_tables: itw[1] carries n^-1), inputs below
+ * 2q.  stage_max[s] = largest |v| / q entering stage s.  Returns 0, or -(s+1) when stage s sees a value above the
+ * schedule. */
+int mfo_fp64_negacyclic_forward(uint64_t *a, int logn, uint64_t q, const uint64_t *tw, double *stage_max) {
+    const size_t n = (size_t)1 << logn;
+    const double qd = (double)q, qinv = 1.0 / qd;
+    double *v = (double *)malloc(n * sizeof(double));
+    for (size_t i = 0; i < n; ++i) v[i] = (double)a[i];
+    int B = 32, rc = 0, s = 0;
+    for (size_t m = 1; m < n; m <<= 1, ++s) {
+        const size_t pairs = n / m / 2;
+        const int fold = (B + fp_t(B) > 64) && (s != logn - 1);
+        double mx = 0;
+        for (size_t i = 0; i < n; ++i) if (fabs(v[i]) > mx) mx = fabs(v[i]);
+        if (stage_max) stage_max[s] = mx / qd;
+        if (mx > (double)B / 16.0 * qd && !rc) rc = -(s + 1);
+        for (size_t k = 0; k < m; ++k) {
+            const double w = centred(tw[m + k], q), wq = w / qd;
+            double *x = v + 2 * k * pairs, *y = x + pairs;
+            for (size_t j = 0; j < pairs; ++j) {
+                double X = x[j];
+                if (fold) X = fp_fold(X, qd, qinv);
+                const double t = fp_mul(y[j], w, wq, qd);
+                y[j] = X - t; x[j] = X + t;
+            }
+        }
+        B = (fold ? 9 : B) + fp_t(B);
+    }
+    for (size_t i = 0; i < n; ++i) a[i] = fp_canon(fp_fold(v[i], qd, qinv), q);
+    free(v);
+    return rc;
+}
+int mfo_fp64_negacyclic_inverse(uint64_t *a, int logn, uint64_t q, const uint64_t *itw, uint64_t n_inv, double *stage_max) {
+    const size_t n = (size_t)1 << logn;
+    const double qd = (double)q, qinv = 1.0 / qd;
+    double *v = (double *)malloc(n * sizeof(double));
+    for (size_t i = 0; i < n; ++i) v[i] = (double)a[i];
+    int B = 32, rc = 0, s = 0;
+    for (size_t m = n / 2; m >= 1; m >>= 1, ++s) {
+        const size_t pairs = n / m / 2;
+        const int fold = 2 * B > 32;
+        double mx = 0;
+        for (size_t i = 0; i < n; ++i) if (fabs(v[i]) > mx) mx = fabs(v[i]);
+        if (stage_max) stage_max[s] = mx / qd;
+        if (mx > (double)B / 16.0 * qd && !rc) rc = -(s + 1);
+        for (size_t k = 0; k < m; ++k) {
+            const double w = centred(itw[m + k], q), wq = w / qd;
+            double *x = v + 2 * k * pairs, *y = x + pairs;
+            for (size_t j = 0; j < pairs; ++j) {
+                const double X = x[j], Y = y[j];
+                if (m == 1) {                               /* last stage: n^-1 on the sums, itw[1] = w * n^-1 on the differences */
+                    const double ni = centred(n_inv, q);
+                    x[j] = fp_mul(X + Y, ni, ni / qd, qd);
+                    y[j] = fp_mul(X - Y, w, wq, qd);
+                } else {
+                    double sum = X + Y;
+                    if (fold) sum = fp_fold(sum, qd, qinv);
+                    x[j] = sum;
+                    y[j] = fp_mul(X - Y, w, wq, qd);
+                }
+            }
+        }
+        const int xb = fold ? 9 : 2 * B, yb = fp_t(2 * B);
+        B = xb > yb ? xb : yb;
+    }
+    for (size_t i = 0; i < n; ++i) a[i] = fp_canon(v[i], q);
+    free(v);
+    return rc;
+}
