@@ -245,6 +245,40 @@ def config2_50bit_block(dev, steps=20):
     return out
 
 
+def link_ceiling(hbuf, dev):
+    """Host <-> device copy rates of this box with the e2e buffers themselves (pinned, 1 GiB): one direction at a time
+    and both at once -- the ceiling the e2e number is read against."""
+    import torch
+    dbuf = torch.empty_like(hbuf, device=dev)
+    dbuf2 = torch.empty_like(hbuf, device=dev)
+    hout = torch.empty_like(hbuf).pin_memory()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    nbytes = hbuf.numel() * hbuf.element_size()
+
+    def timed(fn, reps=3):
+        fn(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps
+
+    def h2d():
+        with torch.cuda.stream(s1):
+            dbuf.copy_(hbuf, non_blocking=True)
+
+    def d2h():
+        with torch.cuda.stream(s2):
+            hout.copy_(dbuf2, non_blocking=True)
+
+    def both():
+        h2d(); d2h()
+
+    return {"h2d_gbs": nbytes / timed(h2d) / 1e9, "d2h_gbs": nbytes / timed(d2h) / 1e9,
+            "both_directions_each_gbs": nbytes / timed(both) / 1e9,
+            "note": "pinned 1 GiB copies, cudaMemcpyAsync on separate streams; e2e moves 2 GiB each way per step"}
+
+
 def gpu_baselines():
     """The two GPU baselines BASELINE.json's north_star names, timed on THIS box in THIS run: the reference's own CUDA
     kernels and Phantom's, i.e. the UNMODIFIED sources of /root/reference compiled for sm_100a by baseline/build_ref.py
@@ -648,6 +682,15 @@ def main():
     e2e_s = float(te.item())
     assert (hnp.reshape(x.shape)[0] == x[0]).all()
     nbytes = x.nbytes
+    try:
+        link = link_ceiling(hbuf, dev)
+        if world > 1:                                       # all ranks copy at once, like the e2e step: slowest rank
+            tl = torch.tensor([link["h2d_gbs"], link["d2h_gbs"], link["both_directions_each_gbs"]], device=dev)
+            dist.all_reduce(tl, op=dist.ReduceOp.MIN)
+            link.update(h2d_gbs=float(tl[0]), d2h_gbs=float(tl[1]), both_directions_each_gbs=float(tl[2]),
+                        ranks="minimum over ranks, all ranks copying at the same time")
+    except Exception as e:                                  # noqa: BLE001
+        link = {"error": repr(e)[:200]}
 
     secondary = None
     if not args.no_secondary:
@@ -683,7 +726,8 @@ def main():
             "e2e": {"value": world * LIMB_POLYS / e2e_s, "unit": "limb-polys/s",
                     "h2d_bytes_per_step": 2 * nbytes, "d2h_bytes_per_step": 2 * nbytes,
                     "ms_per_step": e2e_s * 1e3,
-                    "path": "mfhe_ntt_forward_host + mfhe_ntt_inverse_host on pinned host memory"},
+                    "path": "mfhe_ntt_forward_host + mfhe_ntt_inverse_host on pinned host memory",
+                    "link_gbs_each_way": 2 * nbytes / e2e_s / 1e9, "link_ceiling": link},
             "gpu_launches": 4 * args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak,
