@@ -683,6 +683,7 @@ def main():
     assert (hnp.reshape(x.shape)[0] == x[0]).all()
     nbytes = x.nbytes
     try:
+        barrier()
         link = link_ceiling(hbuf, dev)
         if world > 1:                                       # all ranks copy at once, like the e2e step: slowest rank
             tl = torch.tensor([link["h2d_gbs"], link["d2h_gbs"], link["both_directions_each_gbs"]], device=dev)
