@@ -330,6 +330,17 @@ int mfhe_modup(const mfhe_ntt_plan *qp, const mfhe_bconv_plan *q_to_p, const uin
                void *stream);
 int mfhe_moddown(const mfhe_ntt_plan *qp, const mfhe_bconv_plan *p_to_q, const uint64_t *d_x, uint64_t *d_out,
                  uint64_t *d_scratch, size_t batch, void *stream);
+/* mod-down that allocates nothing and asks no scratch of its caller.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and the same words out as mfhe_moddown; the scratch is a static device array
+ * inside the library (held by every GPU that loads it until exit).  Limit: batch * LP * N <= MFHE_MODDOWN_STATIC_WORDS
+ * (16 MiB), beyond it MFHE_EINVAL with the sizes in mfhe_last_error().  All calls share that one array: calls that overlap
+ * on the GPU (two streams, two unordered threads) race -- keep them on one stream or order them with events.  The first
+ * call on a device resolves the array's device address (do it once before a graph capture); no call uses cudaMalloc,
+ * cudaFree or an allocating library routine. */
+#define MFHE_MODDOWN_STATIC_WORDS ((size_t)1 << 21)
+int mfhe_moddown_static(const mfhe_ntt_plan *qp, const mfhe_bconv_plan *p_to_q, const uint64_t *d_x, uint64_t *d_out,
+                        size_t batch, void *stream);
 
 /* ---- RNS rescale of the matrix scheme (the reference reserves the chain -- delta = 2^35 next to
  * ten 35-bit primes, config.h:25-44 -- and ships only rescale_by_delta_rns, trace.cu:132-161, a multiplication by constants).

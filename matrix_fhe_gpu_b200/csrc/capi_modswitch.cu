@@ -9,6 +9,8 @@
 //   mod-down  [batch][LQ+LP][N] NTT form over Q u P  ->  [batch][LQ][N] NTT form over Q:
 //             out_i = (x_i - NTT(bConv_{P->Q}(INTT(x_P)))_i) * P^-1 mod q_i  =  (x - [x]_P) / P  up to the base
 //             conversion's multiple-of-P slack (|error| < LP, the approximate mod-down of RNS-CKKS / Phantom).
+#include <mutex>
+#include <string>
 #include <vector>
 
 #include "capi_common.h"
@@ -81,4 +83,59 @@ extern "C" int mfhe_moddown(const mfhe_ntt_plan* qp, const mfhe_bconv_plan* p_to
     moddown_combine_kernel<<<grid, 256, 0, st>>>((const u64*)d_x, (u64*)d_out, qp->d_moduli, qp->d_mu, qp->logn, lq, lq + lp, total, k);
     e = cudaGetLastError();
     return e == cudaSuccess ? MFHE_OK : cuda_fail(e, "moddown");
+}
+
+// ---- mod-down without any allocation by anybody -------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  mfhe_moddown needs batch * LP * N words of scratch
+// from its caller; here that scratch is a file-scope device array of a fixed, modest size that every GPU which loads
+// the library holds until the process exits.
+//   * limit: batch * LP * N <= MFHE_MODDOWN_STATIC_WORDS (2^21 words = 16 MiB; e.g. N = 2^16, LP = 4, batch = 8);
+//   * in HOST code `g_moddown_scratch` is only a stand-in for the symbol, not a device address: the address is resolved
+//     with cudaGetSymbolAddress once per device, with that device current, and that pointer is what the kernels get;
+//   * every call shares the one array and it keeps the last call's contents.  Nothing here needs it zeroed: the region a
+//     call uses (its first batch * LP * N words) is overwritten by the copy of the P limbs before anything reads it;
+//   * calls that overlap on the GPU (different streams, or different host threads without ordering) RACE on the array:
+//     serialise them on one stream or with events.
+// The first call on a device resolves the symbol address (it may load the module); make that call before a graph capture.
+namespace {
+constexpr size_t kStaticWords = MFHE_MODDOWN_STATIC_WORDS;
+static __device__ __align__(256) unsigned long long g_moddown_scratch[kStaticWords];
+constexpr int kMaxDevices = 64;
+uint64_t* g_scratch_ptr[kMaxDevices] = {};            // per device: resolved address of g_moddown_scratch
+std::mutex g_scratch_mu;
+
+int static_scratch(uint64_t** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "moddown_static: cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) return fail(MFHE_EUNSUPPORTED, "moddown_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_scratch_mu);
+    if (!g_scratch_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_moddown_scratch);          // this device is current
+        if (e != cudaSuccess || !p) return cuda_fail(e, "moddown_static: cudaGetSymbolAddress");
+        g_scratch_ptr[dev] = (uint64_t*)p;
+    }
+    *out = g_scratch_ptr[dev];
+    return MFHE_OK;
+}
+}  // namespace
+
+extern "C" int mfhe_moddown_static(const mfhe_ntt_plan* qp, const mfhe_bconv_plan* p_to_q, const uint64_t* d_x,
+                                   uint64_t* d_out, size_t batch, void* stream) {
+    if (!qp || !p_to_q || ((!d_x || !d_out) && batch)) return fail(MFHE_EINVAL, "moddown_static: NULL argument");
+    if (batch == 0) return MFHE_OK;
+    int lp = 0, lq = 0;
+    if (mfhe_bconv_plan_sizes(p_to_q, &lp, &lq) != MFHE_OK || lq + lp != qp->L)
+        return fail(MFHE_EINVAL, "moddown_static: the plan's limbs must be the conversion's output base followed by its input base");
+    const size_t N = (size_t)1 << qp->logn;
+    if (batch > kStaticWords / ((size_t)lp * N))
+        return fail(MFHE_EINVAL, "moddown_static: batch * LP * N = " + std::to_string(batch * (size_t)lp * N) +
+                                 " words exceeds the static scratch of " + std::to_string(kStaticWords) +
+                                 " words (16 MiB); use mfhe_moddown with caller scratch");
+    uint64_t* scratch = nullptr;
+    const int rc = static_scratch(&scratch);
+    if (rc != MFHE_OK) return rc;
+    return mfhe_moddown(qp, p_to_q, d_x, d_out, scratch, batch, stream);
 }
