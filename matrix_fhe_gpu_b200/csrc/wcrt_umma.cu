@@ -33,8 +33,13 @@
 #ifndef MFHE_UMMA_PREFETCH
 #define MFHE_UMMA_PREFETCH 1      // chunks ahead of the loads that the producers prefetch into L2 (0.362 -> 0.355 ms)
 #endif
+#ifndef MFHE_UMMA_LOADER_WARP
+#define MFHE_UMMA_LOADER_WARP 0      // 1: the table stream gets a warp of its own.  Measured (profiles/r2_11_wcrt_limiters.txt): barrier-only
+                                     // skeleton 0.205 -> 0.193 ms, product kernel 0.354 -> 0.361 ms: the issuing thread is not the limiter
+#endif
 #ifndef MFHE_UMMA_DBG
-#define MFHE_UMMA_DBG 0      // timing experiments only: 1 = no table copies, 2 = no input loads, 4 = no epilogue arithmetic
+#define MFHE_UMMA_DBG 0      // timing experiments only: 1 = no table copies, 2 = no input loads, 4 = no epilogue arithmetic,
+                             // 16 = producers skip the digit stores, 32 = epilogue skips the TMEM reads, 64 = epilogue keeps TMEM until its stores are done
 #endif
 
 namespace mfhe {
@@ -112,7 +117,10 @@ template <int ND, int SRC> struct UmmaCfg {
     // 96 registers, no spills); the computing sources (int64 reduction, samplers) need two (21 warps, 80 registers)
     static constexpr int PG = (SRC == kSrcMem) ? 1 : 2, PROD_WARPS = 4 * PG;
     static constexpr int ISSUE_WARP = PROD_WARPS + EPI_WARPS;
-    static constexpr int THREADS = (ISSUE_WARP + 1) * 32;
+    // MFHE_UMMA_LOADER_WARP = 1 gives the table stream a warp of its own instead of the issuing thread refilling the ring
+    // (an experiment on whether the ONE issuing thread's serial work per chunk limits the MMA stream: it does not)
+    static constexpr int LOADER_WARP = ISSUE_WARP + 1;
+    static constexpr int THREADS = (ISSUE_WARP + 1 + MFHE_UMMA_LOADER_WARP) * 32;
     static constexpr int NS = (ND <= 5) ? 4 : 3;                       // ring stages
     static constexpr int STAGE = ND * (A_PLANE + B_PLANE);
     // first K step of a tile: if the accumulate / overwrite pieces would not be multiples of 16 columns (ND = 6,
@@ -173,32 +181,46 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const u32 tmem = *tmem_slot;
 
-    if (warp == C::ISSUE_WARP) {
-        // ===== one thread: issues the MMAs and streams the table digits (one bulk copy per digit plane and chunk) =====
-        if (lane == 0) {
-            auto issue_A = [&](int g) {
-                const int s = g % C::NS, kt = g % kchunks;
-                const TileIdx ti = tile_decode((int)blockIdx.x + (g / kchunks) * (int)gridDim.x, nOT, nCB);
-                const unsigned char* base = a.tabt + (size_t)(a.limb0 + a.lz0 + ti.lz) * 8 * a.phi * a.phi;
+    // table digits of chunk g -> its ring stage: one bulk copy per digit plane, completion on the stage's fullA barrier
+    auto issue_A = [&](int g) {
+        const int s = g % C::NS, kt = g % kchunks;
+        const TileIdx ti = tile_decode((int)blockIdx.x + (g / kchunks) * (int)gridDim.x, nOT, nCB);
+        const unsigned char* base = a.tabt + (size_t)(a.limb0 + a.lz0 + ti.lz) * 8 * a.phi * a.phi;
 #if MFHE_UMMA_DBG & 1
-                mbar_arrive(bar_fullA(s)); return;
+        mbar_arrive(bar_fullA(s)); return;
 #endif
-                mbar_expect_tx(bar_fullA(s), ND * A_PLANE);
-                const u32 dst = smem_u32(smem + s * C::STAGE);
+        mbar_expect_tx(bar_fullA(s), ND * A_PLANE);
+        const u32 dst = smem_u32(smem + s * C::STAGE);
 #pragma unroll
-                for (int u = 0; u < ND; ++u)
-                    bulk_g2s(dst + u * A_PLANE,
-                             base + ((size_t)u * a.phi * a.phi) + ((size_t)ti.ot * kchunks + kt) * A_PLANE, A_PLANE, bar_fullA(s));
-            };
-            for (int g = 0; g < C::NS && g < my_chunks; ++g) issue_A(g);
+        for (int u = 0; u < ND; ++u)
+            bulk_g2s(dst + u * A_PLANE,
+                     base + ((size_t)u * a.phi * a.phi) + ((size_t)ti.ot * kchunks + kt) * A_PLANE, A_PLANE, bar_fullA(s));
+    };
+
+    if (MFHE_UMMA_LOADER_WARP && warp == C::LOADER_WARP) {
+        // ===== one thread: streams the table digits, one stage ahead of nothing but the ring itself =====
+        if (lane == 0) {
             for (int g = 0; g < my_chunks; ++g) {
-                const int s = g % C::NS, kt = g % kchunks, it = g / kchunks;
-                const u32 par = (g / C::NS) & 1;
+                if (g >= C::NS) mbar_wait(bar_empty(g % C::NS), ((g / C::NS) - 1) & 1);
+                issue_A(g);
+            }
+        }
+        __syncwarp();
+    } else if (warp == C::ISSUE_WARP) {
+        // ===== one thread: issues the MMAs (and, without a loader warp, refills the ring with table digits) =====
+        if (lane == 0) {
+            if (!MFHE_UMMA_LOADER_WARP)
+                for (int g = 0; g < C::NS && g < my_chunks; ++g) issue_A(g);
+            const u32 smem0 = smem_u32(smem);
+            const u32 idesc_full = C::idesc(ND * UN);
+            int s = 0, kt = 0, it = 0;
+            u32 par = 0;
+            for (int g = 0; g < my_chunks; ++g) {
                 if (kt == 0 && it > 0) mbar_wait(bar_tempty, (it - 1) & 1);      // epilogue has drained the accumulators
                 mbar_wait(bar_fullA(s), par);
                 mbar_wait(bar_fullB(s), par);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const u32 sa = smem_u32(smem + s * C::STAGE), sb = sa + ND * A_PLANE;
+                const u32 sa = smem0 + (u32)s * (u32)C::STAGE, sb = sa + ND * A_PLANE;
 #pragma unroll
                 for (int ks = 0; ks < UKC / 32; ++ks) {
                     const u64 bdesc = umma_desc(sb + ks * 256, 128, 512);
@@ -206,13 +228,13 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                         // first K step of a tile: nothing to accumulate onto.  Position block u+ND-1 is new for
                         // every u, the others were started by u-1: split the instruction accordingly.
                         if constexpr (C::ZERO_FIRST) {
-                            umma_i8(tmem + (u32)((ND - 1) * UN), umma_desc(smem_u32(zpad), 128, 512), bdesc, C::idesc(ND * UN), 0);
-                            umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, C::idesc(ND * UN), 0);
+                            umma_i8(tmem + (u32)((ND - 1) * UN), umma_desc(smem_u32(zpad), 128, 512), bdesc, idesc_full, 0);
+                            umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, idesc_full, 0);
 #pragma unroll
                             for (int u = 1; u < ND; ++u)
-                                umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE, 128, 512), bdesc, C::idesc(ND * UN), 1);
+                                umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE, 128, 512), bdesc, idesc_full, 1);
                         } else {
-                        umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, C::idesc(ND * UN), 0);
+                        umma_i8(tmem, umma_desc(sa, 128, 512), bdesc, idesc_full, 0);
 #pragma unroll
                         for (int u = 1; u < ND; ++u) {
                             const u64 adesc = umma_desc(sa + u * A_PLANE, 128, 512);
@@ -231,17 +253,21 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
 #pragma unroll
                         for (int u = 0; u < ND; ++u)
                             umma_i8(tmem + (u32)(u * UN), umma_desc(sa + u * A_PLANE + ks * 256, 128, 512), bdesc,
-                                    C::idesc(ND * UN), 1);
+                                    idesc_full, 1);
 #endif
                     }
                 }
                 umma_commit(bar_empty(s));
                 if (kt == kchunks - 1) umma_commit(bar_tfull);
-                // while chunk g runs, refill the stage chunk g-1 has just released
-                if (g >= 1 && g - 1 + C::NS < my_chunks) {
-                    mbar_wait(bar_empty((g - 1) % C::NS), ((g - 1) / C::NS) & 1);
-                    issue_A(g - 1 + C::NS);
+                if (!MFHE_UMMA_LOADER_WARP) {
+                    // while chunk g runs, refill the stage chunk g-1 has just released
+                    if (g >= 1 && g - 1 + C::NS < my_chunks) {
+                        mbar_wait(bar_empty((g - 1) % C::NS), ((g - 1) / C::NS) & 1);
+                        issue_A(g - 1 + C::NS);
+                    }
                 }
+                if (++s == C::NS) { s = 0; par ^= 1; }
+                if (++kt == kchunks) { kt = 0; ++it; }
             }
         }
         __syncwarp();
@@ -346,7 +372,9 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             if (more && f_kt == grp) f_tile();                   // (only reads of the OLD f_ok / ic remain below: see order)
 #pragma unroll
             for (int r = 0; r < R; ++r) {
+#if !(MFHE_UMMA_DBG & 16)
                 if (live[r]) stash_item(sB, r, rb[r]);
+#endif
                 if (more) fetch_item(r, rb[r]);
             }
             if (more) f_advance();
@@ -377,10 +405,15 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             for (int sg = 0; sg < 4; ++sg) {
                 if (ccol + 8 * (sg & 1) >= UN) continue;          // last part of a tile whose width is not a multiple of 16
                 u32 acc[2 * ND - 1][4];
+#if MFHE_UMMA_DBG & 32
+#pragma unroll
+                for (int w = 0; w < 2 * ND - 1; ++w) { acc[w][0] = lane + w; acc[w][1] = lane ^ w; acc[w][2] = sg; acc[w][3] = it; }
+#else
 #pragma unroll
                 for (int w = 0; w < 2 * ND - 1; ++w)
                     tmem_ld_16x256(tlane + ((u32)(16 * (sg >> 1)) << 16) + (u32)(w * UN + ccol + 8 * (sg & 1)), acc[w]);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#endif
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     u64 lo = acc[0][e], up = acc[5 < 2 * ND - 1 ? 5 : 0][e];
