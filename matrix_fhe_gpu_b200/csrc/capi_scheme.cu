@@ -728,6 +728,11 @@ extern "C" int mfhe_ct_matmul(mfhe_ctx* c, const uint64_t* ctU_re, const uint64_
     if (!c || !ctU_re || !ctU_im || !ctV_re || !ctV_im || !out) return fail(MFHE_EINVAL, "ct_matmul: NULL argument");
     const size_t T = c->T();
     cudaError_t e = cudaSuccess;
+    // MFHE_MATMUL_PATH: unset = tcgen05 kernel when the shape allows it; m = the four mma.sync GEMMs (trace_tc.cu)
+    const char* path = std::getenv("MFHE_MATMUL_PATH");
+    if (!(path && path[0] == 'm') && ct_matmul_umma_eligible(c->n, c->L, c->ndig.data()))
+        return done(ct_matmul_umma_launch((const u64*)ctU_re, (const u64*)ctU_im, (const u64*)ctV_re, (const u64*)ctV_im, (u64*)out, T,
+                                          c->d_moduli, c->d_mu, c->ndig.data(), c->L, c->phi, S(s)), "ct_matmul");
     for (int k = 0; k < 4 && e == cudaSuccess; ++k) {
         const size_t uo = (k & 1) ? T : 0, vo = (k & 2) ? T : 0;      // k: 0 bb, 1 ab, 2 ba, 3 aa
         e = gemm_ty(c, (const u64*)ctU_re + uo, (const u64*)ctU_im + uo, (const u64*)ctV_re + vo, (const u64*)ctV_im + vo,

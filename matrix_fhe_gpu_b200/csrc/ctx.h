@@ -180,6 +180,10 @@ cudaError_t rescale_combine_launch(const u64* in, u64* out, const u64* moduli, c
                                    const RescaleConsts& k, cudaStream_t st);
 cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                        const RescaleConsts& k, cudaStream_t st);
+// the four GEMMs of mfhe_ct_matmul in one tcgen05 kernel (ct_matmul_umma.cu)
+bool ct_matmul_umma_eligible(int n, int limbs, const int* h_ndig);
+cudaError_t ct_matmul_umma_launch(const u64* Ure, const u64* Uim, const u64* Vre, const u64* Vim, u64* out, size_t T,
+                                  const u64* moduli, const ulonglong2* mu, const int* h_ndig, int limbs, int phi, cudaStream_t st);
 bool trace_gemm_tc_eligible(int n, int limbs, const int* h_ndig);
 cudaError_t trace_gemm_tc_launch(const u64* Ar, const u64* Ai, const u64* Bpr, const u64* Bpi, u64* Cr, u64* Ci,
                                  const u64* moduli, const ulonglong2* mu, const int* h_ndig, int limbs, int batch,

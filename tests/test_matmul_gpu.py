@@ -110,3 +110,27 @@ def test_encrypted_matmul_native_shape(cuda_device):
     print(f"encrypted matmul native shape: max_err {err:.3e}, entries up to {np.abs(want).max():.1f}")
     assert err <= 2.0 ** -20 * np.abs(want).max()
     assert np.abs(R[0] - V[0].conj().T).max() < 1e-4 and np.abs(R[1] - U[1]).max() < 1e-4
+
+
+def test_ct_matmul_tcgen05_equals_mma_sync_native_shape(cuda_device, monkeypatch):
+    """mfhe_ct_matmul at the native shape (512 lanes, L = 11: ten 5-digit limbs and one 6-digit limb): the tcgen05 kernel
+    (ct_matmul_umma.cu: stacked M = 128, digit-stack instructions, TMEM accumulators) against the four mma.sync GEMMs of
+    trace_tc.cu, every word of the 8 poly sets; extreme residues (0, q - 1) included; twice (persistent CTAs reuse TMEM)."""
+    import torch
+    import matrix_fhe_gpu_b200.scheme as S
+    g = S.Context()
+    q = dev(np.repeat(np.asarray(g.moduli, dtype=np.uint64), g.n2)[None].repeat(g.phi, 0).reshape(-1), cuda_device)
+    cts = []
+    for seed in range(4):
+        a = g.sample_uniform()
+        x = torch.cat([(a * (3 + seed) + seed) % q, (a * (7 + seed) + 1) % q])       # [b | a] halves, canonical residues
+        x[:64] = 0
+        x[64:128] = q[64:128] - 1
+        x[g.T + 128:g.T + 192] = q[128:192] - 1
+        cts.append(x)
+    monkeypatch.setenv("MFHE_MATMUL_PATH", "m")
+    ref = g.ct_matmul(*cts).clone()
+    monkeypatch.delenv("MFHE_MATMUL_PATH")
+    for _ in range(2):
+        got = g.ct_matmul(*cts)
+        assert torch.equal(got, ref)
