@@ -14,21 +14,26 @@
 // instruction for A's digit u accumulates at TMEM column 32 u, so position w = u + v collects every digit pair with one
 // instruction per (u, K step):  4 column blocks x 4 K steps x ND instructions per GEMM.
 //
-// CTA (persistent, one per SM, 256 threads) per problem:
+// CTA (persistent, one per SM, 512 threads) per problem:
 //   stage A  : 2 components x (re, im) x 64 x 64 words -> ND planes [128 m][128 k] in the UMMA canonical K-major layout
 //              (8 x 16-byte core matrices); the contraction index y is the SLOW index of the ciphertext matrices, so lanes
 //              run along x (coalesced 256-byte segments) and a thread packs four consecutive y into one 32-bit store per plane
 //   per vc   : stage B' = digit stacks of the four column blocks (each V word lands twice: Vr in the Dr and Di columns,
 //              Vi and q - Vi once each), then per column block: one thread issues the 4 ND instructions, commits to an
-//              mbarrier; all 8 warps read the 2ND-1 partial sums of their 32 rows x 16 columns from TMEM, recombine to 128
+//              mbarrier; all 16 warps read the 2ND-1 partial sums of their 32 rows x 8 columns from TMEM, recombine to 128
 //              bits, multiply by n (shift), ONE Barrett reduction, 32-byte stores.
 #include "ctx.h"
 #include "modmath.cuh"
 
+#ifndef MFHE_MM_DBG
+#define MFHE_MM_DBG 0      // timing experiments only: 1 = no global loads while staging, 2 = no epilogue, 4 = no MMAs, 8 = no digit stores
+#endif
 namespace mfhe {
 
 namespace {
-constexpr int CN = 64, CM = 128, CK = 128, CUN = 32, CTH = 256;
+constexpr int CN = 64, CM = 128, CK = 128, CUN = 32, CTH = 512;
+constexpr int SR = 16 / (CTH / 64);                  // staging rounds: 16 four-k groups per row over CTH / 64 thread groups
+constexpr int EC = CUN / (CTH / 128);                // epilogue: columns per thread (TMEM lane quarter = warp % 4)
 constexpr int PLANE = CM * CK;                       // 16 KiB: one digit plane of A (128 rows x 128 k)
 
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
@@ -56,8 +61,10 @@ __device__ __forceinline__ void umma_i8(u32 d_tmem, u64 adesc, u64 bdesc, u32 id
 __device__ __forceinline__ void umma_commit(u32 bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void tmem_ld4(u32 taddr, u32 (&r)[4]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+// 16 lanes x 256 bits: thread T gets lane T/4 (r0, r1) and lane T/4 + 8 (r2, r3), columns 2 (T%4), 2 (T%4) + 1 of the
+// 8-column group (cute Copy_Traits<SM100_TMEM_LOAD_16dp256b1x>)
+__device__ __forceinline__ void tmem_ld_16x256(u32 taddr, u32 (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
 }
 
@@ -77,6 +84,15 @@ __device__ __forceinline__ void digits4(const u64 (&x)[4], u32 (&w)[ND]) {
     }
 }
 
+// s0 + 2^8 s1 + 2^16 s2 + 2^24 s3 + 2^32 s4 for partial sums below 2^28 (result below 2^61)
+__device__ __forceinline__ u64 fold5(u32 s0, u32 s1, u32 s2, u32 s3, u32 s4) {
+    u64 r = ((u64)s4 << 32) | s0;
+    asm("mad.wide.u32 %0, %1, 256, %0;" : "+l"(r) : "r"(s1));
+    asm("mad.wide.u32 %0, %1, 65536, %0;" : "+l"(r) : "r"(s2));
+    asm("mad.wide.u32 %0, %1, 16777216, %0;" : "+l"(r) : "r"(s3));
+    return r;
+}
+
 struct MatmulLimbs { int cnt; int limbs; unsigned char l[64]; };
 
 template <int ND>
@@ -85,7 +101,7 @@ struct MmCfg {
     static constexpr int BBLK = NP * CK;                         // bytes of one column block's digit stack
     static constexpr int SMEM = ND * PLANE + 4 * BBLK + 256;     // A planes + 4 column blocks + barrier / TMEM slot
     static constexpr int ACC = (2 * ND - 1) * CUN;               // TMEM columns in use
-    static_assert(ACC <= 512 && NP <= 256 && NP % 16 == 0, "tile width");
+    static_assert(ACC <= 512 && NP <= 256 && NP % 16 == 0 && EC == 8, "tile width");
 };
 
 template <int ND>
@@ -126,8 +142,10 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
     for (int prob = blockIdx.x; prob < nprob; prob += gridDim.x) {
         const int w = prob / ll.cnt, l = ll.l[prob % ll.cnt];
         const size_t base = ((size_t)w * ll.limbs + l) * CN * CN;
-        const u64 q = moduli[l];
+        const u64 q = moduli[l], q2 = 2 * q;
         const ulonglong2 mu = mu_tab[l];
+        const int kb = 64 - __clzll((long long)q);
+        const u64 mu1 = (mu.y << (kb - 2)) | (mu.x >> (66 - kb));              // floor(2^128 / q) >> (66 - k) = floor(2^(k+62) / q)
 
         // ---- A = [U_b ; U_a]: row m = 64 c + x, k = y (re) / 64 + y (im) ----
 #pragma unroll 1
@@ -135,11 +153,15 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             const u64* sr = Ure + c * T + base;
             const u64* si = Uim + c * T + base;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int kq = ((t >> 6) ^ rot) + 4 * r;                       // y = 4 kq .. 4 kq + 3
+            for (int r = 0; r < SR; ++r) {
+                const int kq = (((t >> 6) & 3) ^ rot) + 4 * ((t >> 8) + (CTH / 256) * r);   // y = 4 kq .. 4 kq + 3
                 u64 xr[4], xi[4];
 #pragma unroll
+#if MFHE_MM_DBG & 1
+                for (int j = 0; j < 4; ++j) { xr[j] = (u64)(kq + j + t); xi[j] = (u64)(kq * j + t); }
+#else
                 for (int j = 0; j < 4; ++j) { xr[j] = sr[(4 * kq + j) * CN + sx]; xi[j] = si[(4 * kq + j) * CN + sx]; }
+#endif
                 u32 wr[ND], wi[ND];
                 digits4<ND>(xr, wr); digits4<ND>(xi, wi);
                 const u32 o_r = canon(64 * c + sx, 4 * kq), o_i = canon(64 * c + sx, 64 + 4 * kq);
@@ -158,12 +180,16 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             const u64* sr = Vre + vc * T + base;
             const u64* si = Vim + vc * T + base;
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                const int kq = ((t >> 6) ^ rot) + 4 * r;
+            for (int r = 0; r < SR; ++r) {
+                const int kq = (((t >> 6) & 3) ^ rot) + 4 * ((t >> 8) + (CTH / 256) * r);
                 u64 xr[4], xi[4], xn[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
+#if MFHE_MM_DBG & 1
+                    xr[j] = (u64)(kq + j + t); xi[j] = (u64)(kq * j + t);
+#else
                     xr[j] = sr[(4 * kq + j) * CN + sx]; xi[j] = si[(4 * kq + j) * CN + sx];
+#endif
                     xn[j] = q - xi[j];
                 }
                 u32 wr[ND], wi[ND], wn[ND];
@@ -183,74 +209,115 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy stores -> visible to the MMA
             __syncthreads();
 
+            // one thread: the 4 ND instructions of column block cb, then a commit on the block barrier
+            auto issue = [&](int cb) {
+#if MFHE_MM_DBG & 4
+                return;
+#endif
+                if (t != 0) return;
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const u32 a0 = smem_u32(sA), b0 = smem_u32(sB + cb * C::BBLK);
+#pragma unroll
+                for (int ks = 0; ks < CK / 32; ++ks) {
+                    const u64 bdesc = umma_desc(b0 + ks * 256);
+                    if (ks == 0) {
+                        // nothing to accumulate onto: position block u + ND - 1 is new for every u, the others were
+                        // started by u - 1 -- accumulate piece + overwrite piece
+                        umma_i8(tmem, umma_desc(a0), bdesc, idesc(C::NP), 0);
+#pragma unroll
+                        for (int u = 1; u < ND; ++u) {
+                            const u64 adesc = umma_desc(a0 + u * PLANE);
+                            umma_i8(tmem + (u32)(u * CUN), adesc, bdesc, idesc((ND - 1) * CUN), 1);
+                            umma_i8(tmem + (u32)((u + ND - 1) * CUN), adesc, umma_desc(b0 + (ND - 1) * (CUN / 8) * 1024),
+                                    idesc(CUN), 0);
+                        }
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < ND; ++u)
+                            umma_i8(tmem + (u32)(u * CUN), umma_desc(a0 + u * PLANE + ks * 256), bdesc, idesc(C::NP), 1);
+                    }
+                }
+                umma_commit(bar);
+            };
+
 #pragma unroll 1
             for (int cb = 0; cb < 4; ++cb) {
-                if (t == 0) {
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const u32 a0 = smem_u32(sA), b0 = smem_u32(sB + cb * C::BBLK);
-#pragma unroll
-                    for (int ks = 0; ks < CK / 32; ++ks) {
-                        const u64 bdesc = umma_desc(b0 + ks * 256);
-                        if (ks == 0) {
-                            // nothing to accumulate onto: position block u + ND - 1 is new for every u, the others were
-                            // started by u - 1 -- accumulate piece + overwrite piece
-                            umma_i8(tmem, umma_desc(a0), bdesc, idesc(C::NP), 0);
-#pragma unroll
-                            for (int u = 1; u < ND; ++u) {
-                                const u64 adesc = umma_desc(a0 + u * PLANE);
-                                umma_i8(tmem + (u32)(u * CUN), adesc, bdesc, idesc((ND - 1) * CUN), 1);
-                                umma_i8(tmem + (u32)((u + ND - 1) * CUN), adesc, umma_desc(b0 + (ND - 1) * (CUN / 8) * 1024),
-                                        idesc(CUN), 0);
-                            }
-                        } else {
-#pragma unroll
-                            for (int u = 0; u < ND; ++u)
-                                umma_i8(tmem + (u32)(u * CUN), umma_desc(a0 + u * PLANE + ks * 256), bdesc, idesc(C::NP), 1);
-                        }
-                    }
-                    umma_commit(bar);
-                }
+                // block cb's MMAs were issued before the previous block's reductions (or just above, for cb = 0)
+                if (cb == 0) issue(0);
+#if !(MFHE_MM_DBG & 4)
                 mbar_wait(bar, phase);
                 phase ^= 1;
+#endif
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-                // ---- epilogue: thread = output row m = 32 (warp % 4) + lane, 16 columns (warp / 4) of the block ----
-                const int m = 32 * (warp & 3) + lane, c = m >> 6, x = m & 63;
+                // ---- epilogue: warp = TMEM lane quarter (warp % 4) x 8 columns (warp / 4).  The 16x256b load shape gives a thread
+                // rows lane/4 and lane/4 + 8 of a 16-row half and the column pair 2 (lane % 4): four threads share a row, so
+                // one store instruction writes 64-byte row segments (8 lines) instead of 32 scattered 16-byte pieces ----
+                const int c = (warp & 3) >> 1;                                  // rows 0..63: U's b component, 64..127: a
                 const int ri = cb >> 1;                                         // 0: real part, 1: imaginary part
-                u64* o = out + (size_t)(2 * (c + 2 * vc) + ri) * T + base + (size_t)x * CN + (cb & 1) * 32 + (warp >> 2) * 16;
-                const u32 trow = tmem + ((u32)(32 * (warp & 3)) << 16) + (u32)((warp >> 2) * 16);
+                u64* o = out + (size_t)(2 * (c + 2 * vc) + ri) * T + base + (size_t)(32 * (warp & 1) + (lane >> 2)) * CN
+                         + (cb & 1) * 32 + (warp >> 2) * EC + 2 * (lane & 3);
+                const u32 trow = tmem + ((u32)(32 * (warp & 3)) << 16) + (u32)((warp >> 2) * EC);
+#if MFHE_MM_DBG & 2
+                if (q == 12345) o[0] = trow;
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads();
+                if (cb < 3) issue(cb + 1);
+#else
+                // phase 1 (holds TMEM): value = n * sum_w S_w 2^(8w) with S_w < 2^27 is folded into
+                //   vlo = sum_{w<5} S_w 2^(8w)  (< 2^60),   vup = sum_{5<=w<10} S_w 2^(8(w-5)),   [vtop = S_10 for six digits]
+                u64 vlo[EC], vup[EC];
+                u32 vtop[(2 * ND - 1 > 10) ? EC : 1];
+                u32 acc[2][2 * ND - 1][4];                                      // loads of half 1 fly while half 0 is folded
 #pragma unroll
-                for (int grp = 0; grp < 4; ++grp) {
-                    u32 acc[2 * ND - 1][4];
+                for (int p = 0; p < 2 * ND - 1; ++p) tmem_ld_16x256(trow + (u32)(p * CUN), acc[0][p]);
 #pragma unroll
-                    for (int p = 0; p < 2 * ND - 1; ++p) tmem_ld4(trow + (u32)(p * CUN + 4 * grp), acc[p]);
+                for (int grp = 0; grp < 2; ++grp) {                             // 16-row halves of the lane quarter
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    u64 res[4];
+                    if (grp == 0) {
+#pragma unroll
+                        for (int p = 0; p < 2 * ND - 1; ++p) tmem_ld_16x256(trow + (16u << 16) + (u32)(p * CUN), acc[1][p]);
+                    }
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        u64 lo = 0, hi = 0;
+                        // S_0 + 2^8 S_1 + 2^16 S_2 + 2^24 S_3 as three 32 x 32 + 64 multiply-adds, 2^32 S_4 into the high word
+                        const u32 (&a)[2 * ND - 1][4] = acc[grp & 1];
+                        u64 lo = fold5(a[0][e], a[1][e], a[2][e], a[3][e], 2 * ND - 1 > 4 ? a[2 * ND - 1 > 4 ? 4 : 0][e] : 0u);
+                        u64 up = 0;
+                        if constexpr (2 * ND - 1 > 5)
+                            up = fold5(a[5][e], 2 * ND - 1 > 6 ? a[2 * ND - 1 > 6 ? 6 : 0][e] : 0u, 2 * ND - 1 > 7 ? a[2 * ND - 1 > 7 ? 7 : 0][e] : 0u,
+                                       2 * ND - 1 > 8 ? a[2 * ND - 1 > 8 ? 8 : 0][e] : 0u, 2 * ND - 1 > 9 ? a[2 * ND - 1 > 9 ? 9 : 0][e] : 0u);
+                        vlo[4 * grp + e] = lo; vup[4 * grp + e] = up;
+                        if constexpr (2 * ND - 1 > 10) vtop[4 * grp + e] = acc[grp & 1][10][e];
+                    }
+                }
+                // the accumulators are in registers: the next column block's MMAs run under the reductions below
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads();
+                if (cb < 3) issue(cb + 1);
+                // phase 2: value < 64 * 128 * q^2 < 2^(k+62) for k = bits(q) <= 48, so the ONE-word Barrett of the W-CRT
+                // epilogue applies: qhat = mulhi(v >> (k-2), floor(2^(k+62) / q)) is within 2 of the quotient (HAC 14.42)
 #pragma unroll
-                        for (int p = 0; p < 2 * ND - 1; ++p) {
-                            const u64 s = (u64)acc[p][e];
-                            const int sh = 8 * p;
-                            if (sh < 64) {
-                                const u64 xs = s << sh;
-                                lo += xs; hi += (lo < xs);
-                                if (sh > 32) hi += s >> (64 - sh);
-                            } else {
-                                hi += s << (sh - 64);
-                            }
-                        }
+                for (int e = 0; e < EC; e += 2) {
+                    u64 res[2];
+#pragma unroll
+                    for (int k2 = 0; k2 < 2; ++k2) {
+                        const u64 xs = vup[e + k2] << 40;
+                        u64 lo = vlo[e + k2] + xs;
+                        u64 hi = (vup[e + k2] >> 24) + (lo < xs);
+                        if constexpr (2 * ND - 1 > 10) hi += (u64)vtop[e + k2] << 16;
                         hi = (hi << 6) | (lo >> 58);                            // times n = 64
                         lo <<= 6;
-                        res[e] = reduce128(lo, hi, q, mu.x, mu.y);
+                        const u64 x1 = (lo >> (kb - 2)) | (hi << (66 - kb));
+                        const u64 rr = lo - __umul64hi(x1, mu1) * q;
+                        res[k2] = csub(csub(rr, q2), q);
                     }
-                    *reinterpret_cast<ulonglong2*>(o + 4 * grp) = make_ulonglong2(res[0], res[1]);
-                    *reinterpret_cast<ulonglong2*>(o + 4 * grp + 2) = make_ulonglong2(res[2], res[3]);
+                    // e = 4 half + 2 hf: row 16 half + 8 hf (+ lane / 4), the thread's column pair
+                    *reinterpret_cast<ulonglong2*>(o + (size_t)(16 * (e >> 2) + 8 * ((e >> 1) & 1)) * CN) = make_ulonglong2(res[0], res[1]);
                 }
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                __syncthreads();                                                // accumulators drained; B' of vc still in use
+#endif
             }
+            __syncthreads();                                                    // every warp is done with this vc's B' stacks
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
