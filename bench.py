@@ -115,7 +115,7 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
                                        "kernel": "wcrt_umma_kernel (tcgen05.mma kind::i8), profiles/r1_12_ncu_umma_summary.txt"}
             del a_u
             # encrypted matrix product: four Gaussian-integer GEMMs on the ciphertext components
-            # (mma.sync u8 digit GEMMs, K = 2n) + the 4-term decryption
+            # (one tcgen05 kind::i8 kernel, U components stacked to M = 128, K = 2n) + the 4-term decryption
             prod = g.ct_matmul(cr, ci, cr, ci)
             ms_mm = timed(lambda: g.ct_matmul(cr, ci, cr, ci), 3)
             ms_md = timed(lambda: g.ct_matmul_decrypt(prod, sk), 3)
@@ -128,7 +128,11 @@ def secondary_metrics(dev, world, dist, pairs_per_rank=2, with_cpu=False):
                              "achieved": 16 * g.T * 8 / (ms_mm * 1e-3) / 1e9, "peak": peaks()[0], "unit": "GB/s",
                              "frac": 16 * g.T * 8 / (ms_mm * 1e-3) / 1e9 / peaks()[0],
                              "int8_macs_per_s": macs_mm / (ms_mm * 1e-3),
-                             "note": "ct_matmul: 4 x (read 4 S + write 2 S); legacy mma.sync path, the tcgen05 form is the W-CRT's"}}
+                             "tensor_frac": macs_mm / (ms_mm * 1e-3) / 2.25e15,
+                             "note": "ct_matmul_umma_kernel (tcgen05.mma kind::i8, TMEM accumulators): reads the 8 operand "
+                                     "poly sets once, writes the 8 product poly sets; tensor_frac against the nominal 2.25 P "
+                                     "int8 MAC/s the MMA stream itself reaches (profiles/r2_11_wcrt_limiters.txt); "
+                                     "MFHE_MATMUL_PATH=m selects the four mma.sync GEMMs (2.5 ms)"}}
             del prod
             zero = torch.zeros_like(sk)
             ct_r, ct_i = g.allocate_ciphertext(), g.allocate_ciphertext()

@@ -25,6 +25,9 @@
 #include "ctx.h"
 #include "modmath.cuh"
 
+#ifndef MFHE_MM_PREFETCH
+#define MFHE_MM_PREFETCH 1
+#endif
 #ifndef MFHE_MM_DBG
 #define MFHE_MM_DBG 0      // timing experiments only: 1 = no global loads while staging, 2 = no epilogue, 4 = no MMAs, 8 = no digit stores
 #endif
@@ -66,6 +69,15 @@ __device__ __forceinline__ void umma_commit(u32 bar) {
 __device__ __forceinline__ void tmem_ld_16x256(u32 taddr, u32 (&r)[4]) {
     asm volatile("tcgen05.ld.sync.aligned.16x256b.x1.b32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
+
+// a (re, im) pair of 64 x 64 matrices (2 x 32 KiB = 512 lines) towards L2, one line per thread: what the NEXT staging step
+// reads, so that its loads find the lines on their way
+__device__ __forceinline__ void prefetch_pair(const u64* re, const u64* im) {
+#if MFHE_MM_PREFETCH
+    const u64* p = (threadIdx.x < 256 ? re : im) + (threadIdx.x & 255) * 16;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#endif
 }
 
 // byte offset of (row, k) inside a K-major canonical operand whose rows hold 128 k
@@ -152,6 +164,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
         for (int c = 0; c < 2; ++c) {
             const u64* sr = Ure + c * T + base;
             const u64* si = Uim + c * T + base;
+            if (c == 1) prefetch_pair(Vre + base, Vim + base);
 #pragma unroll
             for (int r = 0; r < SR; ++r) {
                 const int kq = (((t >> 6) & 3) ^ rot) + 4 * ((t >> 8) + (CTH / 256) * r);   // y = 4 kq .. 4 kq + 3
@@ -179,6 +192,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             //      Column block cb = n / 32, stack row = 32 v + n % 32 ----
             const u64* sr = Vre + vc * T + base;
             const u64* si = Vim + vc * T + base;
+            if (vc == 0) prefetch_pair(Vre + T + base, Vim + T + base);
 #pragma unroll
             for (int r = 0; r < SR; ++r) {
                 const int kq = (((t >> 6) & 3) ^ rot) + 4 * ((t >> 8) + (CTH / 256) * r);
@@ -244,6 +258,11 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             for (int cb = 0; cb < 4; ++cb) {
                 // block cb's MMAs were issued before the previous block's reductions (or just above, for cb = 0)
                 if (cb == 0) issue(0);
+                if (vc == 1 && cb < 2 && prob + (int)gridDim.x < nprob) {       // the next problem's U components
+                    const int p2 = prob + (int)gridDim.x;
+                    const size_t b2 = ((size_t)(p2 / ll.cnt) * ll.limbs + ll.l[p2 % ll.cnt]) * CN * CN;
+                    prefetch_pair(Ure + cb * T + b2, Uim + cb * T + b2);
+                }
 #if !(MFHE_MM_DBG & 4)
                 mbar_wait(bar, phase);
                 phase ^= 1;
