@@ -29,10 +29,11 @@ def rand_sets(rng, o, count):
     return out
 
 
-@pytest.mark.parametrize("n,f,bits,L", [(64, 5, 45, 3), (64, 5, 35, 2), (16, 5, 45, 5), (32, 17, 50, 2)])
+@pytest.mark.parametrize("n,f,bits,L", [(64, 5, 45, 3), (64, 5, 35, 2), (64, 5, 30, 2), (64, 5, 48, 1), (16, 5, 45, 5), (32, 17, 50, 2)])
 def test_matmul_pieces_bit_exact_vs_oracle(cuda_device, n, f, bits, L):
-    """n = 64 runs the tensor-core GEMM with transposed operand staging (trace_tc.cu, 6- and 5-digit moduli), the other
-    shapes the CUDA-core kernel; 50-bit moduli (7 digits) exercise the CUDA-core fallback's range."""
+    """n = 64 runs the tensor-core kernels -- mfhe_trace_gemm_ty on trace_tc.cu (mma.sync, transposed operand staging),
+    mfhe_ct_matmul on ct_matmul_umma.cu (tcgen05) -- with 6-, 5- and 4-digit moduli (48 / 45, 35, 30 bits); the other shapes
+    the CUDA-core kernel; 50-bit moduli (7 digits) exercise the CUDA-core fallback's range."""
     import matrix_fhe_gpu_b200.scheme as S
     mods = O.primes_congruent_one(2 * n * 3 * f, bits, L)
     g = S.Context(n, f, mods, 2.0 ** 30)
