@@ -13,3 +13,6 @@ wc -l gpurun_out/launches_r2.csv
 ncu --set full --clock-control none --import-source on -k regex:"ntt_(cols|rows)" -s 12 -c 4 -o gpurun_out/prof_ntt_r2 -f \
     python bench.py --steps 2 --warmup 3 --no-cpu --no-baselines --no-secondary --no-config5 --e2e-steps 1 > gpurun_out/ncu_full_r2.log 2>&1
 ls -la gpurun_out/prof_ntt_r2.ncu-rep
+ncu --set full --clock-control none --import-source on -k regex:ct_matmul_umma -c 2 -o gpurun_out/prof_matmul_r2 -f \
+    python tools/time_matmul.py > gpurun_out/ncu_matmul_r2.log 2>&1
+ls -la gpurun_out/prof_matmul_r2.ncu-rep
