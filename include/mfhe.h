@@ -293,7 +293,9 @@ int mfhe_trace_gemm_ty(mfhe_ctx *ctx, const uint64_t *d_Ur, const uint64_t *d_Ui
 int mfhe_transpose(mfhe_ctx *ctx, const uint64_t *d_in, uint64_t *d_out, size_t count, void *stream);
 /* trace.cu:132-161 repaired: limb l is multiplied by h_inv[l] (HOST array of L constants) */
 int mfhe_trace_rescale_limbs(mfhe_ctx *ctx, uint64_t *d_Cr, uint64_t *d_Ci, int batch, const uint64_t *h_inv, void *stream);
-/* the four component GEMMs of two ciphertext pairs; d_out = 8 poly sets [bb re, im | ab re, im | ba re, im | aa re, im] */
+/* the four component GEMMs of two ciphertext pairs; d_out = 8 poly sets [bb re, im | ab re, im | ba re, im | aa re, im],
+ * each [w][l][x][z].  n = 64 and moduli below 2^48: one tcgen05 kernel (csrc/ct_matmul_umma.cu); otherwise four GEMMs of
+ * the mfhe_trace_gemm_ty kind (MFHE_MATMUL_PATH=m forces those). */
 int mfhe_ct_matmul(mfhe_ctx *ctx, const uint64_t *d_ctU_re, const uint64_t *d_ctU_im, const uint64_t *d_ctV_re,
                    const uint64_t *d_ctV_im, uint64_t *d_out, void *stream);
 /* decrypts the 4-component product (d_prod is consumed as scratch); out = evals [w][l][z][x] of n * sum_y U V' */
