@@ -746,6 +746,12 @@ extern "C" int mfhe_ct_matmul_decrypt(mfhe_ctx* c, uint64_t* prod, const uint64_
     const size_t T = c->T();
     u64* D = (u64*)prod;
     cudaStream_t st = S(s);
+    // n = 64: one kernel per (lane, limb) matrix with R1, R2 in shared memory (scheme.cu); MFHE_MATMUL_DECRYPT_PATH=r keeps
+    // the sequence of row-kernel passes and transposes below (any n)
+    const char* dpath = std::getenv("MFHE_MATMUL_DECRYPT_PATH");
+    if (c->n == 64 && !(dpath && dpath[0] == 'r'))
+        return done(matmul_decrypt_launch(D, T, (const u64*)sk, (u64*)out_re, (u64*)out_im, c->xy_plan->small_rows(), c->d_mu,
+                                          c->phi, c->L, st), "ct_matmul_decrypt");
     auto rows = [&](const u64* mr, const u64* mi, const u64* ar, const u64* ai, u64* o_r, u64* o_i) {
         RowArgs r;                                      // (o_r, o_i) = (mr, mi) + (ar, ai) (*) s along the fast index
         r.a = ar; r.a1 = ai; r.s = (const u64*)sk; r.m0 = mr; r.o0 = o_r; r.m1 = mi; r.o1 = o_i;

@@ -162,6 +162,9 @@ struct RowArgs {                 // one launch over all phi*L*n rows of n coeffi
 };
 struct SmallTables;
 cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulonglong2* mu, cudaStream_t st);
+// fused decryption of the 8 poly sets of mfhe_ct_matmul (n = 64): out = evals [w][l][z][x]
+cudaError_t matmul_decrypt_launch(const u64* D, size_t T, const u64* sk, u64* out_re, u64* out_im, const SmallTables& Tb,
+                                  const ulonglong2* mu, int phi, int limbs, cudaStream_t st);
 cudaError_t sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi, cudaStream_t st);
 // sampler_sound.cu: kind 0 uniform [w][l][y][x], 1 gaussian (same), 2 ternary [w][l][x]
 cudaError_t sound_sample_launch(int kind, u64* out, const u64* moduli, const ulonglong2* mu, int n, int limbs, int phi,

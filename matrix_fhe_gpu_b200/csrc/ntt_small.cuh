@@ -19,12 +19,14 @@ struct SmallNet {
     static_assert(FP2 == 0 && PL <= 6, "n <= 256");
 
     // natural-order row g -> canonical values at bit-reversed-order positions 8u .. 8u+7
+    // gstride: distance (in words) between consecutive coefficients of the source row (1 = a contiguous row; the fused
+    // matrix-product decryption transforms COLUMNS of a shared-memory tile)
     __device__ static __forceinline__ void forward(u64 (&v)[8], const u64* __restrict__ g, u64* sm, u32 u,
-                                                   const tw_t* __restrict__ tw, u64 q, u64 q2) {
+                                                   const tw_t* __restrict__ tw, u64 q, u64 q2, u32 gstride = 1) {
         {
             const u32 e0 = deposit3(u, FP0);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = g[e0 + (j << FP0)];
+            for (int j = 0; j < 8; ++j) v[j] = g[(e0 + (j << FP0)) * gstride];
             fwd_pass<LOGN, FP0, 7>(v, e0, tw, q, q2);
             if constexpr (FP0 > 0) {
 #pragma unroll
@@ -55,12 +57,12 @@ struct SmallNet {
     // with |v| <= fp_fwd_out_bound(LOGN) q/16 at the same positions; inverse_fp takes doubles with |v| <= 2q and returns
     // canonical residues exactly like inverse().
     __device__ static __forceinline__ void forward_fp(u64 (&v)[8], const u64* __restrict__ g, u64* sm, u32 u,
-                                                      const tw_t* __restrict__ tw, const fconst_t& c) {
+                                                      const tw_t* __restrict__ tw, const fconst_t& c, u32 gstride = 1) {
         u64 (&V)[1][8] = reinterpret_cast<u64 (&)[1][8]>(v);
         {
             const u32 e0 = deposit3(u, FP0);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = u_of(fp_load(g[e0 + (j << FP0)]));
+            for (int j = 0; j < 8; ++j) v[j] = u_of(fp_load(g[(e0 + (j << FP0)) * gstride]));
             fwd_pass<LOGN, FP0, 7, 1, fconst_t>(V, e0, tw, c);
             if constexpr (FP0 > 0) {
 #pragma unroll

@@ -123,6 +123,102 @@ cudaError_t xrow_mul_s_launch(const RowArgs& r, const SmallTables& T, const ulon
     return cudaGetLastError();
 }
 
+// ---- fused decryption of the 4-component matrix product (mfhe_ct_matmul_decrypt, n = 64) ---------------------------
+//   out[z][x] = R1[x][z] + (R2[., z] (*)_x s)[x],   R1 = D_bb + D_ba (*)_z s,   R2 = D_ab + D_aa (*)_z s      (re and im alike)
+// One CTA per (lane, limb) matrix, a row of 64 per 8 threads as in xrow_mul_s.  The two inner convolutions run along the
+// fast index of the product's [x][z] matrices and leave R1, R2 in shared memory; the outer one runs along x, i.e. down
+// the COLUMNS of the R2 tile (stride ld in shared memory -- the transposes of the unfused path cost nothing here), and
+// its result goes out as rows of [z][x].  Reads the 8 product poly sets once and writes 2, against 26 poly-set passes of
+// the unfused sequence (3 row-kernel launches + 4 transposes); same words.
+template <int AR>
+__global__ void __launch_bounds__(512, 1)
+matmul_decrypt_kernel(const u64* __restrict__ D, size_t T, const u64* __restrict__ sk, u64* __restrict__ out_re,
+                      u64* __restrict__ out_im, SmallTables Tb, const ulonglong2* __restrict__ mu_tab, int limbs) {
+    using Net = SmallNet<6>;
+    constexpr int N = 64, LD = N + 1, STRIDE = Net::STRIDE;
+    extern __shared__ __align__(16) u64 sm_md[];
+    u64* R = sm_md;                                   // [4][64][LD]: R1 re, R1 im, R2 re, R2 im
+    u64* snet = sm_md + 4 * N * LD;                   // [64][STRIDE]: the networks' exchange tiles, one per row
+    const u32 u = threadIdx.x & 7, row = threadIdx.x >> 3;
+    const u32 wl = blockIdx.x, l = wl % limbs;
+    const size_t base = (size_t)wl * N * N;
+    const u64 q = Tb.moduli[l], q2 = 2 * q;
+    const ulonglong2 mu = mu_tab[l];
+    u64* sm = snet + row * STRIDE;
+    const tw_t* tw = Tb.tw + ((size_t)l << 6);
+    const tw_t* itw = Tb.itw + ((size_t)l << 6);
+    const tw_t ninv = Tb.ninv[l], w1n = Tb.w1n[l];
+    // key words of this thread's network positions 8u .. 8u+7 (stored in the same bit-reversed order)
+    u64 sv[8];
+    {
+        const u64* s = sk + ((size_t)wl << 6) + 8 * u;
+        const ulonglong2 s0 = __ldg((const ulonglong2*)s), s1 = __ldg((const ulonglong2*)s + 1),
+                         s2 = __ldg((const ulonglong2*)s + 2), s3 = __ldg((const ulonglong2*)s + 3);
+        sv[0] = s0.x; sv[1] = s0.y; sv[2] = s1.x; sv[3] = s1.y; sv[4] = s2.x; sv[5] = s2.y; sv[6] = s3.x; sv[7] = s3.y;
+    }
+    // v <- INTT(NTT(src) (.) s), canonical, v[j] = coefficient  e + (j << PL)  (e returned)
+    auto conv = [&](u64 (&v)[8], const u64* src, u32 stride) -> u32 {
+        u32 e;
+        if constexpr (AR) {
+            const fconst_t fc = make_fconst(q);
+            Net::forward_fp(v, src, sm, u, tw, fc, stride);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = u_of(fp_mul_generic(fp_fold(d_of(v[j]), fc), fp_load(sv[j]), fc));
+            e = Net::inverse_fp(v, sm, u, itw, fc, ninv, w1n);
+        } else {
+            Net::forward(v, src, sm, u, tw, q, q2, stride);
+            const barrett1_t bc = make_barrett1(q, mu.x, mu.y);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = mul_barrett1(v[j], sv[j], bc);
+            e = Net::inverse(v, sm, u, itw, q, q2, ninv, w1n);
+        }
+        __syncwarp();                                  // the row's exchange tile is reused by the next transform
+        return e;
+    };
+    // inner convolutions along z: k = 0, 1 -> R1 (re, im) from (D_bb, D_ba); k = 2, 3 -> R2 from (D_ab, D_aa)
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+        const u64* m = D + (size_t)(k < 2 ? k : k) * T + base + (size_t)row * N;           // D_bb re, im | D_ab re, im = sets 0..3
+        const u64* a = D + (size_t)(4 + k) * T + base + (size_t)row * N;                   // D_ba re, im | D_aa re, im = sets 4..7
+        u64 v[8];
+        const u32 e = conv(v, a, 1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const u32 pos = e + (j << Net::PL);
+            R[(k * N + row) * LD + pos] = add_mod(m[pos], v[j], q);
+        }
+    }
+    __syncthreads();
+    // outer convolution along x, this thread group's row is now z = row: column z of R2, added to column z of R1
+#pragma unroll 1
+    for (int ri = 0; ri < 2; ++ri) {
+        u64 v[8];
+        const u32 e = conv(v, R + (size_t)(2 + ri) * N * LD + row, LD);
+        u64* o = (ri ? out_im : out_re) + base + (size_t)row * N;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const u32 pos = e + (j << Net::PL);
+            o[pos] = add_mod(R[(ri * N + pos) * LD + row], v[j], q);
+        }
+    }
+}
+
+cudaError_t matmul_decrypt_launch(const u64* D, size_t T, const u64* sk, u64* out_re, u64* out_im, const SmallTables& Tb,
+                                  const ulonglong2* mu, int phi, int limbs, cudaStream_t st) {
+    constexpr int smem = (4 * 64 * 65 + 64 * SmallNet<6>::STRIDE) * (int)sizeof(u64);
+    cudaError_t e;
+    if (Tb.arith) {
+        e = cudaFuncSetAttribute(matmul_decrypt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        matmul_decrypt_kernel<1><<<(unsigned)(phi * limbs), 512, smem, st>>>(D, T, sk, out_re, out_im, Tb, mu, limbs);
+    } else {
+        e = cudaFuncSetAttribute(matmul_decrypt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        matmul_decrypt_kernel<0><<<(unsigned)(phi * limbs), 512, smem, st>>>(D, T, sk, out_re, out_im, Tb, mu, limbs);
+    }
+    return cudaGetLastError();
+}
+
 // ---- samplers (stand-alone form; encrypt fuses them into the W-CRT loader, wcrt.cu) -------------------
 __device__ __forceinline__ u64 splitmix64_s(u64 x) {
     x += 0x9E3779B97F4A7C15ULL;

@@ -135,3 +135,29 @@ def test_ct_matmul_tcgen05_equals_mma_sync_native_shape(cuda_device, monkeypatch
     for _ in range(2):
         got = g.ct_matmul(*cts)
         assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("L", [11, 3])
+def test_ct_matmul_decrypt_fused_equals_pass_sequence(cuda_device, monkeypatch, L):
+    """mfhe_ct_matmul_decrypt at n = 64: the fused kernel (R1, R2 in shared memory, the outer convolution down the columns
+    of the tile; scheme.cu) against the sequence of three row-kernel passes and four transposes, every word, on both
+    arithmetics of the row networks (FP64 pipe / integer)."""
+    import torch
+    import matrix_fhe_gpu_b200.scheme as S
+    g = S.Context(moduli=S.REF_MODULI[:L])
+    q = dev(np.repeat(np.asarray(g.moduli, dtype=np.uint64), g.n2)[None].repeat(g.phi, 0).reshape(-1), cuda_device)
+    a = g.sample_uniform()
+    prod = torch.cat([(a * (k + 2) + k) % q for k in range(8)])
+    prod[:64] = 0
+    prod[4 * g.T:4 * g.T + 64] = q[:64] - 1
+    prod[6 * g.T + 64:6 * g.T + 128] = q[64:128] - 1
+    sk = g.generate_secret_key()
+    monkeypatch.setenv("MFHE_MATMUL_DECRYPT_PATH", "r")
+    ref = [t.clone() for t in g.ct_matmul_decrypt(prod.clone(), sk)]
+    monkeypatch.delenv("MFHE_MATMUL_DECRYPT_PATH")
+    for arith in (1, 0):
+        g.set_row_arith(arith)
+        for _ in range(2):
+            got = g.ct_matmul_decrypt(prod.clone(), sk)
+            assert torch.equal(got[0], ref[0]) and torch.equal(got[1], ref[1]), arith
+    g.set_row_arith(1)
