@@ -298,7 +298,8 @@ int mfhe_trace_rescale_limbs(mfhe_ctx *ctx, uint64_t *d_Cr, uint64_t *d_Ci, int 
  * the mfhe_trace_gemm_ty kind (MFHE_MATMUL_PATH=m forces those). */
 int mfhe_ct_matmul(mfhe_ctx *ctx, const uint64_t *d_ctU_re, const uint64_t *d_ctU_im, const uint64_t *d_ctV_re,
                    const uint64_t *d_ctV_im, uint64_t *d_out, void *stream);
-/* decrypts the 4-component product (d_prod is consumed as scratch); out = evals [w][l][z][x] of n * sum_y U V' */
+/* decrypts the 4-component product; out = evals [w][l][z][x] of n * sum_y U V'.  d_prod may be used as scratch (it is for
+ * n != 64; the fused n = 64 kernel only reads it): treat it as consumed */
 int mfhe_ct_matmul_decrypt(mfhe_ctx *ctx, uint64_t *d_prod, const uint64_t *d_sk, uint64_t *d_out_re, uint64_t *d_out_im, void *stream);
 
 /* ---- multi-GPU: limb-sharded base conversion (BASELINE config 5).  One process per GPU.  The exchange
