@@ -178,7 +178,7 @@ matmul_decrypt_kernel(const u64* __restrict__ D, size_t T, const u64* __restrict
     // inner convolutions along z: k = 0, 1 -> R1 (re, im) from (D_bb, D_ba); k = 2, 3 -> R2 from (D_ab, D_aa)
 #pragma unroll 1
     for (int k = 0; k < 4; ++k) {
-        const u64* m = D + (size_t)(k < 2 ? k : k) * T + base + (size_t)row * N;           // D_bb re, im | D_ab re, im = sets 0..3
+        const u64* m = D + (size_t)k * T + base + (size_t)row * N;                         // D_bb re, im | D_ab re, im = sets 0..3
         const u64* a = D + (size_t)(4 + k) * T + base + (size_t)row * N;                   // D_ba re, im | D_aa re, im = sets 4..7
         u64 v[8];
         const u32 e = conv(v, a, 1);
