@@ -1,6 +1,7 @@
 // intpipe.cu -- issue-rate micro-benchmark for the integer work of a 64-bit NTT butterfly on B200.
 // "the first artefact to produce on the box".  Build + run:
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o intpipe intpipe.cu && ./intpipe
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -DMFHE_MODMUL=0 -o intpipe intpipe.cu && ./intpipe
+// (-DMFHE_MODMUL=0: the FP64-assisted quotient variants measured here need the prepared-twiddle form of modmath.cuh)
 // Each kernel keeps ILP independent dependency chains per thread in registers; results are
 // folded into one store so nothing is optimised away.  Reported: lane-ops per clock per SM
 // (using the SM clock measured inside the kernel with clock64 / globaltimer).
