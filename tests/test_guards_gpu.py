@@ -130,3 +130,63 @@ def test_canaries_and_determinism_flat_family(cuda_device, logn, limbs, batch):
         bc.partial_scatter(xin, 0, len(q), [sc.view.data_ptr() + 8 * j * N for j in range(len(p))], [len(p) * N] * len(p), N, batch)
         torch.cuda.synchronize()
         assert out.intact() and sc.intact() and torch.equal(sc.view, o0)
+
+
+def test_canaries_and_determinism_round2_kernels(cuda_device):
+    """The kernels added late in round 2: tcgen05 encrypted matrix product (persistent CTAs, TMEM reuse across problems, an
+    mbarrier per column block), its fused decryption (shared-memory tiles read down their columns), the FP64-pipe NTT
+    kernels, and the mod-down on the static scratch.  Outputs between canaries, 12 runs on the same input, same words."""
+    import torch
+    import matrix_fhe_gpu_b200 as m
+    import matrix_fhe_gpu_b200.scheme as S
+    from matrix_fhe_gpu_b200 import check, _dev_ptr, _stream_handle
+    L_ = S._L()
+    g = S.Context(64, 5, O.primes_congruent_one(2 * 64 * 15, 45, 1) + O.primes_congruent_one(2 * 64 * 15, 35, 2), 2.0 ** 30)
+    T = g.T
+    cts = [Guarded(2 * T, cuda_device, torch.cat([g.sample_uniform(), g.sample_gaussian()])) for _ in range(4)]
+    prod = Guarded(8 * T, cuda_device)
+    o_re, o_im = Guarded(T, cuda_device), Guarded(T, cuda_device)
+    sk = g.generate_secret_key()
+    first = None
+    for _ in range(12):
+        prod.view.fill_(-1); o_re.view.fill_(-1); o_im.view.fill_(-1)
+        check(L_.mfhe_ct_matmul(g._h, *[_dev_ptr(c.view) for c in cts], _dev_ptr(prod.view), _stream_handle()))
+        p = prod.view.clone()
+        check(L_.mfhe_ct_matmul_decrypt(g._h, _dev_ptr(prod.view), _dev_ptr(sk), _dev_ptr(o_re.view), _dev_ptr(o_im.view), _stream_handle()))
+        cur = (p, o_re.view.clone(), o_im.view.clone())
+        first = first or cur
+        assert all(torch.equal(x, y) for x, y in zip(first, cur)), "matrix product / decryption is not deterministic"
+    assert all(c.intact() for c in cts) and prod.intact() and o_re.intact() and o_im.intact()
+    q = torch.from_numpy(np.repeat(np.asarray(g.moduli, dtype=np.int64), g.n2)[None].repeat(g.phi, 0).reshape(-1)).to(cuda_device)
+    assert int(first[0].min()) >= 0 and bool((first[0].view(8, T) < q).all())            # canonical residues everywhere
+    # FP64-pipe flat NTT (moduli below 2^50), PB groups + remainder
+    for logn, limbs, batch in ((12, 3, 5), (16, 2, 3), (17, 1, 1)):
+        N = 1 << logn
+        mods = [int(v) for v in O.coeff_modulus_create(N, 50, limbs)]
+        plan = m.NttPlan(logn, mods)
+        assert plan.arith == 1
+        x = dev(O.synth_polys(2, batch, mods, N), cuda_device).reshape(-1)
+        buf = Guarded(x.numel(), cuda_device, x)
+        plan.forward_(buf.view)
+        f0 = buf.view.clone()
+        for _ in range(11):
+            buf.view.copy_(x); plan.forward_(buf.view)
+            assert torch.equal(buf.view, f0), "FP64-pipe forward NTT is not deterministic"
+        plan.inverse_(buf.view)
+        assert torch.equal(buf.view, x) and buf.intact()
+    # mod-down on the library's static scratch
+    import ctypes as C
+    L_.mfhe_moddown_static.argtypes = [C.c_void_p] * 4 + [C.c_size_t, C.c_void_p]
+    logn, lq, lp, batch = 12, 3, 2, 4
+    N = 1 << logn
+    primes = [int(v) for v in O.get_primes(2 * N, 55, lq + lp)]
+    plan, conv = m.NttPlan(logn, primes), S.BconvPlan(primes[lq:], primes[:lq])
+    y = Guarded(batch * (lq + lp) * N, cuda_device, dev(O.synth_polys(5, batch, primes, N), cuda_device).reshape(-1))
+    out = Guarded(batch * lq * N, cuda_device)
+    first = None
+    for _ in range(12):
+        out.view.fill_(-1)
+        check(L_.mfhe_moddown_static(plan._h, conv._h, _dev_ptr(y.view), _dev_ptr(out.view), batch, _stream_handle()))
+        first = out.view.clone() if first is None else first
+        assert torch.equal(out.view, first), "static mod-down is not deterministic"
+    assert y.intact() and out.intact()
