@@ -140,6 +140,9 @@ bconv_kernel(const u64* __restrict__ in, u64* __restrict__ out, size_t N, int l_
     }
 }
 
+}  // namespace
+#include "bconv_umma.cuh"
+namespace {
 __global__ void bconv_reduce_kernel(const u64* __restrict__ parts, u64* __restrict__ out, size_t per_part, int nparts,
                                     size_t N, int out_start, int out_count, const u64* __restrict__ p,
                                     const ulonglong2* __restrict__ mu_p, size_t part_stride) {
@@ -228,7 +231,6 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
             if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
         if (e != cudaSuccess) return cuda_fail(e, who);
     }
-    dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
     // one-word Barrett iff sum_i y_i c_i < in_count * qmax * p_j < 2^(k_j + 61) for every j: in_count * qmax <= 2^61
     uint64_t qmax = 0;
     for (int i = in_start; i < in_start + in_count; ++i) qmax = std::max(qmax, b->q[i]);
@@ -237,6 +239,42 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     const bool w1 = !force128 && (unsigned __int128)qmax * (unsigned)in_count <= ((unsigned __int128)1 << 61);
     static const BconvScatter none{};
     const BconvScatter& tab = sc ? *sc : none;
+    // tensor-core form (bconv_umma.cuh) whenever the coefficient count tiles by 128; MFHE_BCONV_PATH=c keeps the CUDA-core kernels
+    const char* path = getenv("MFHE_BCONV_PATH");
+    // It pays from about 16 input limbs on (B200, N = 2^17, 16 output limbs, batch 16, ms per conversion; profiles/r2_14_bconv_umma.txt):
+    //   input limbs      6      8      12     16     24     48
+    //   CUDA cores     0.23   0.28   0.37   0.46   0.66   2.41 (no register-resident form beyond 24 limbs)
+    //   tensor cores   0.44   0.44   0.44   0.44   0.53   0.72
+    // below that the digit recombination (NDA + NDB - 1 partial sums per output) and the per-tile hand-offs cost more than the
+    // few multiply-accumulates they replace.  MFHE_BCONV_PATH=t forces the tensor-core kernel for any window, =c the CUDA cores.
+    const bool force_t = path && path[0] == 't';
+    if (N % UB_M == 0 && !(path && path[0] == 'c') && !generic && (in_count > 16 || force_t)) {
+        uint64_t pmax = 0;
+        for (uint64_t v : b->p) pmax = std::max(pmax, v);
+        UbArgs a;
+        a.in = (const u64*)in; a.out = (u64*)out; a.N = N; a.l_in_total = b->l_in; a.in_start = in_start; a.in_count = in_count;
+        a.l_out = b->l_out; a.q = b->d_q; a.qhat_inv = b->d_qhat_inv; a.qhat_mod_p = b->d_qhat_mod_p; a.p = b->d_p; a.mu_p = b->d_mu_p;
+        a.nda = ub_digits(qmax - 1); a.ndb = ub_digits(pmax - 1); a.kp = (in_count + 31) / 32 * 32;
+        a.tiles_per_item = (int)(N / UB_M); a.ntiles = (int)(batch * (N / UB_M));
+        const int smem = a.nda * UB_M * a.kp + a.ndb * UB_UN * a.kp + 512;
+        if (smem <= 220 * 1024 && batch * (N / UB_M) < (1u << 30)) {
+            int sms = 0, dev = 0;
+            cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            const int grid1 = std::min(a.ntiles, 2 * sms);
+            cudaError_t e = cudaSuccess;
+#define MFHE_UB_LAUNCH(SCV, W1V)                                                                                              \
+            do {                                                                                                              \
+                e = cudaFuncSetAttribute(bconv_umma_kernel<SCV, W1V>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);        \
+                if (e == cudaSuccess) bconv_umma_kernel<SCV, W1V><<<grid1, UB_TH, smem, (cudaStream_t)stream>>>(a, tab);         \
+            } while (0)
+            if (sc) { if (w1) MFHE_UB_LAUNCH(true, true); else MFHE_UB_LAUNCH(true, false); }
+            else    { if (w1) MFHE_UB_LAUNCH(false, true); else MFHE_UB_LAUNCH(false, false); }
+#undef MFHE_UB_LAUNCH
+            if (e == cudaSuccess) e = cudaGetLastError();
+            return e == cudaSuccess ? MFHE_OK : cuda_fail(e, who);
+        }
+    }
+    dim3 grid((unsigned)((N + BC - 1) / BC), (unsigned)batch);
 #define MFHE_BCONV_LAUNCH(SCV, W1V, ICV)                                                                                   \
     bconv_kernel<SCV, W1V, ICV><<<grid, BC, (ICV) ? 0 : (size_t)in_count * BC * 8, (cudaStream_t)stream>>>(                  \
         (const u64*)in, (u64*)out, N, b->l_in, in_start, in_count, b->l_out, b->d_q, b->d_qhat_inv, b->d_qhat_mod_p, b->d_p,  \

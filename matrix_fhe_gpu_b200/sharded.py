@@ -31,6 +31,7 @@ go through the C ABI and need the GPU.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Sequence, Tuple
 
 
@@ -205,7 +206,10 @@ class LimbShardedBconv:
         import torch
         self.plan_q.inverse_(x)
         lin = len(self.q)
-        win = next((w for w in (24, 16, 12, 8) if lin > w and lin % w == 0), 0)
+        # more than 16 input limbs and N a multiple of 128: one mfhe_bconv call runs on the tensor cores (bconv_umma.cuh,
+        # 0.72 ms at 48 -> 16 limbs against 2 x 0.66 ms + reduce for the window form below)
+        tensor = lin > 16 and self.n % 128 == 0 and os.environ.get("MFHE_BCONV_PATH", "") != "c"
+        win = 0 if tensor else next((w for w in (24, 16, 12, 8) if lin > w and lin % w == 0), 0)
         if win:
             # the register-resident, one-word-Barrett forms of the conversion kernel exist for windows of 2..24 input
             # limbs (bconv.cu); a wider base is converted window by window and the partial sums (already reduced mod

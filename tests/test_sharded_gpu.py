@@ -83,9 +83,10 @@ def test_partial_scatter_matches_partial_plus_exchange(cuda_device, logn, l_in, 
 
 
 @pytest.mark.parametrize("logn,l_in,l_out,bits,batch", [(12, 48, 4, 55, 2), (12, 32, 3, 55, 1), (12, 7, 3, 58, 2)])
-def test_unsharded_step_windows(cuda_device, logn, l_in, l_out, bits, batch):
-    """world = 1: the conversion of a wide base runs window by window on the register-resident kernel forms (48 = 2 x 24,
-    32 = 2 x 16) + mfhe_bconv_reduce, a base without such a split (7) through one mfhe_bconv: both equal the oracle."""
+def test_unsharded_step_windows(cuda_device, monkeypatch, logn, l_in, l_out, bits, batch):
+    """world = 1: a wide base is converted by one mfhe_bconv on the tensor cores (bconv_umma.cuh); with MFHE_BCONV_PATH=c
+    window by window on the register-resident CUDA-core forms (48 = 2 x 24, 32 = 2 x 16) + mfhe_bconv_reduce, a base
+    without such a split (7) through one mfhe_bconv: all equal the oracle."""
     import torch
     from matrix_fhe_gpu_b200 import sharded as S
     N = 1 << logn
@@ -93,6 +94,9 @@ def test_unsharded_step_windows(cuda_device, logn, l_in, l_out, bits, batch):
     q, p = primes[:l_in], primes[l_in:]
     x = O.synth_polys(17, batch, q, N)
     sh = S.LimbShardedBconv(logn, q, p, 0, 1)
+    got = sh.step_unsharded(torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
+    assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
+    monkeypatch.setenv("MFHE_BCONV_PATH", "c")
     got = sh.step_unsharded(torch.from_numpy(x.view(np.int64).copy()).to(cuda_device), batch)
     assert (got.cpu().numpy().view(np.uint64) == _oracle_step(x, logn, q, p)).all()
 
