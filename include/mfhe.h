@@ -97,7 +97,8 @@ int mfhe_ntt_inverse_host(mfhe_ntt_plan *plan, uint64_t *h_data, size_t batch);
  * intermediate stays in L2 (0 = whole batch in one pair of launches). */
 int mfhe_ntt_plan_set_chunk(mfhe_ntt_plan *plan, size_t chunk_limb_polys);
 
-/* Arithmetic of the flat transforms (N = 2^12..2^17).  0: 64-bit integer butterflies (any modulus below 2^60).
+/* Arithmetic of the transforms (flat N = 2^12..2^17 and the n <= 256 networks, all conventions).  0: 64-bit integer
+ * butterflies (any modulus below 2^60).
  * 1: butterflies on the FP64 pipe -- exact, same results word for word -- available when every modulus of the plan is
  * below 2^50 (SURVEY config 2's 50-bit run, the 35/45-bit moduli of the matrix scheme) and then the default; inputs
  * must be below 2q.  MFHE_NTT_ARITH=int in the environment keeps new plans on 0.  set_arith returns MFHE_EUNSUPPORTED

@@ -93,7 +93,7 @@ extern "C" int mfhe_ntt_plan_create(int logn, int L, const uint64_t* moduli, int
     // keeps the integer kernels, mfhe_ntt_plan_set_arith switches a plan
     uint64_t qmax = 0;
     for (int l = 0; l < L; ++l) qmax = std::max(qmax, moduli[l]);
-    if ((flat || convention == MFHE_NTT_PHANTOM_NEGACYCLIC) && qmax < (1ull << 50)) {
+    if (qmax < (1ull << 50)) {
         if ((e = cudaMalloc((void**)&p->d_twd, n * L * sizeof(tw_t))) != cudaSuccess ||
             (e = cudaMalloc((void**)&p->d_itwd, n * L * sizeof(tw_t))) != cudaSuccess ||
             (e = cudaMalloc((void**)&p->d_ninvd, L * sizeof(tw_t))) != cudaSuccess ||
@@ -115,7 +115,7 @@ extern "C" int mfhe_ntt_plan_create(int logn, int L, const uint64_t* moduli, int
 extern "C" int mfhe_ntt_plan_arith(const mfhe_ntt_plan* p) { return p ? p->arith : MFHE_EINVAL; }
 extern "C" int mfhe_ntt_plan_set_arith(mfhe_ntt_plan* p, int arith) {
     if (!p || (arith != 0 && arith != 1)) return fail(MFHE_EINVAL, "set_arith: 0 (integer) or 1 (FP64 pipe)");
-    if (arith && !p->d_twd) return fail(MFHE_EUNSUPPORTED, "set_arith: the FP64-pipe arithmetic needs every modulus below 2^50 (and the Phantom negacyclic convention for n <= 256)");
+    if (arith && !p->d_twd) return fail(MFHE_EUNSUPPORTED, "set_arith: the FP64-pipe arithmetic needs every modulus of the plan below 2^50");
     p->arith = arith;
     return MFHE_OK;
 }

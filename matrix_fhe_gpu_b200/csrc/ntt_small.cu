@@ -24,7 +24,8 @@ constexpr int kSmallThreads = 256;
 
 template <int LOGN> __device__ __forceinline__ u32 bitrev_n(u32 x) { return __brev(x) >> (32 - LOGN); }
 
-template <int LOGN, bool NATURAL>
+// AR = 1: butterflies on the FP64 pipe (every modulus below 2^50, T carries the {w, w/q} tables; modmath.cuh) -- same words
+template <int LOGN, bool NATURAL, int AR>
 __global__ void __launch_bounds__(kSmallThreads)
 ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
     using Net = SmallNet<LOGN>;
@@ -38,7 +39,14 @@ ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t li
     u64* g = data + (lp << LOGN);
     u64* sm = sm_all + pib * STRIDE;
     u64 v[8];
-    Net::forward(v, g, sm, u, T.tw + ((size_t)limb << LOGN), q, q2);
+    if constexpr (AR) {
+        const fconst_t fc = make_fconst(q);
+        Net::forward_fp(v, g, sm, u, T.tw + ((size_t)limb << LOGN), fc);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = fp_store(fp_fold(d_of(v[j]), fc), fc);
+    } else {
+        Net::forward(v, g, sm, u, T.tw + ((size_t)limb << LOGN), q, q2);
+    }
     // the thread now holds positions 8u .. 8u+7 of the bit-reversed-order result
     if constexpr (NATURAL) {
         __syncwarp();
@@ -55,7 +63,7 @@ ntt_small_fwd_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t li
     asm volatile("st.global.v4.u64 [%0], {%1,%2,%3,%4};" ::"l"(g + 8 * u + 4), "l"(v[4]), "l"(v[5]), "l"(v[6]), "l"(v[7]) : "memory");
 }
 
-template <int LOGN, bool NATURAL>
+template <int LOGN, bool NATURAL, int AR>
 __global__ void __launch_bounds__(kSmallThreads)
 ntt_small_inv_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t limb_polys) {
     using Net = SmallNet<LOGN>;
@@ -82,7 +90,15 @@ ntt_small_inv_kernel(u64* __restrict__ data, SmallTables T, int limbs, size_t li
             v[2 * k] = t.x; v[2 * k + 1] = t.y;
         }
     }
-    const u32 e = Net::inverse(v, sm, u, T.itw + ((size_t)limb << LOGN), q, q2, T.ninv[limb], T.w1n[limb]);
+    u32 e;
+    if constexpr (AR) {
+        const fconst_t fc = make_fconst(q);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = u_of(fp_load(v[j]));
+        e = Net::inverse_fp(v, sm, u, T.itw + ((size_t)limb << LOGN), fc, T.ninv[limb], T.w1n[limb]);
+    } else {
+        e = Net::inverse(v, sm, u, T.itw + ((size_t)limb << LOGN), q, q2, T.ninv[limb], T.w1n[limb]);
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[e + (j << Net::PL)] = v[j];
 }
@@ -92,13 +108,17 @@ static cudaError_t launch_small(bool fwd, bool natural, u64* data, const SmallTa
                                 size_t limb_polys, cudaStream_t st) {
     constexpr int PPB = kSmallThreads / ((1 << LOGN) / 8);
     const unsigned grid = (unsigned)((limb_polys + PPB - 1) / PPB);
+#define MFHE_SMALL_LAUNCH(K, NAT)                                                                       \
+    do {                                                                                                \
+        if (T.arith) K<LOGN, NAT, 1><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);         \
+        else         K<LOGN, NAT, 0><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);         \
+    } while (0)
     if (fwd) {
-        if (natural) ntt_small_fwd_kernel<LOGN, true><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
-        else         ntt_small_fwd_kernel<LOGN, false><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+        if (natural) MFHE_SMALL_LAUNCH(ntt_small_fwd_kernel, true); else MFHE_SMALL_LAUNCH(ntt_small_fwd_kernel, false);
     } else {
-        if (natural) ntt_small_inv_kernel<LOGN, true><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
-        else         ntt_small_inv_kernel<LOGN, false><<<grid, kSmallThreads, 0, st>>>(data, T, limbs, limb_polys);
+        if (natural) MFHE_SMALL_LAUNCH(ntt_small_inv_kernel, true); else MFHE_SMALL_LAUNCH(ntt_small_inv_kernel, false);
     }
+#undef MFHE_SMALL_LAUNCH
     return cudaGetLastError();
 }
 

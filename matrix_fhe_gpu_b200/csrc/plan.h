@@ -25,14 +25,12 @@ struct mfhe_ntt_plan {
         return arith ? NttTables{d_moduli, d_twd, d_itwd, d_ninvd, d_w1nd, logn, L, 1}
                      : NttTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, logn, L, 0};
     }
+    // n <= 256: the same merged network for all three conventions, on the FP64 pipe when `arith` (every modulus < 2^50)
     SmallTables small() const {
+        if (arith) return SmallTables{d_moduli, d_twd, d_itwd, d_ninvd, d_w1nd, nullptr, nullptr, logn, L, convention, 1};
         return SmallTables{d_moduli, d_tw, d_itw, d_ninv, d_w1n, nullptr, nullptr, logn, L, convention, 0};
     }
-    // the fused encrypt / decrypt row kernel (scheme.cu) can run its transforms on the FP64 pipe
-    SmallTables small_rows() const {
-        if (arith && convention == MFHE_NTT_PHANTOM_NEGACYCLIC)
-            return SmallTables{d_moduli, d_twd, d_itwd, d_ninvd, d_w1nd, nullptr, nullptr, logn, L, convention, 1};
-        return small();
-    }
+    // the fused encrypt / decrypt row kernels (scheme.cu) use the negacyclic tables
+    SmallTables small_rows() const { return small(); }
 };
 

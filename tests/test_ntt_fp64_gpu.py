@@ -41,7 +41,8 @@ def test_arith_selection(m, cuda_device, monkeypatch):
     assert m.NttPlan(12, O.coeff_modulus_create(n, 50, 2)).arith == 0
     monkeypatch.delenv("MFHE_NTT_ARITH")
     assert m.NttPlan(6, [17592186435073]).arith == 1              # n <= 256: the flag drives the fused row kernel of the scheme
-    assert m.NttPlan(6, [17592186435073], convention=m.GL_XN_MINUS_I).arith == 0
+    assert m.NttPlan(6, [17592186435073], convention=m.GL_XN_MINUS_I).arith == 1   # all three conventions share the network
+    assert m.NttPlan(6, [1152921504606830593 - 0], convention=m.PHANTOM_NEGACYCLIC).arith == 0   # a 60-bit modulus
 
 
 @pytest.mark.parametrize("logn,bits,limbs,batch", [

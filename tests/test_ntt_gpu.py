@@ -201,11 +201,30 @@ def test_small_transforms_all_conventions(m, cuda_device, logn, conv):
         for b in range(batch):
             for l in range(L):
                 f(ref[b, l], n, int(mods[l]))
-    d = to_dev(x, cuda_device)
-    plan.forward_(d)
-    assert (to_host(d) == ref).all()
-    plan.inverse_(d)
-    assert (to_host(d) == x).all()
+    assert plan.arith == 1                               # moduli below 2^50: the FP64-pipe networks are the default
+    for arith in (1, 0):                                 # both arithmetics against the oracle, every word
+        plan.set_arith(arith)
+        d = to_dev(x, cuda_device)
+        plan.forward_(d)
+        assert (to_host(d) == ref).all(), arith
+        plan.inverse_(d)
+        assert (to_host(d) == x).all(), arith
+    # extreme residues through the FP64-pipe networks
+    plan.set_arith(1)
+    q = np.asarray(mods, dtype=np.uint64).reshape(1, L, 1)
+    for fill in (np.zeros_like(x), np.broadcast_to(q - np.uint64(1), x.shape).copy()):
+        want = fill.copy()
+        if conv == 0:
+            want = O.PhantomTables(logn, mods).forward(fill)
+        else:
+            for b in range(batch):
+                for l in range(L):
+                    f(want[b, l], n, int(mods[l]))
+        d = to_dev(fill, cuda_device)
+        plan.forward_(d)
+        assert (to_host(d) == want).all()
+        plan.inverse_(d)
+        assert (to_host(d) == fill).all()
 
 
 def test_reference_driver_patterns_n64(m, cuda_device):
