@@ -310,7 +310,15 @@ __global__ void ct_mul_kernel(const u64* __restrict__ c1, const u64* __restrict_
     const int l = ct_limb(idx, n, limbs, ref_index);
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
     const u64 b1 = c1[idx], a1 = c1[T + idx], b2 = c2[idx], a2 = c2[T + idx];
-    if ((b1 | a1 | b2 | a2) < q || (b1 < q && a1 < q && b2 < q && a2 < q)) {
+    if (q < (1ull << 50) && b1 < q && a1 < q && b2 < q && a2 < q) {
+        // canonical operands of a modulus below 2^50: the four products on the FP64 pipe (exact, modmath.cuh), which leaves
+        // this pass to the memory system (integer form: 56 % of HBM, multiplier-bound)
+        const fconst_t fc = make_fconst(q);
+        const double B1 = fp_load(b1), A1 = fp_load(a1), B2 = fp_load(b2), A2 = fp_load(a2);
+        d0[idx] = fp_store(fp_mul_generic(B1, B2, fc), fc);
+        d1[idx] = fp_store(fp_fold(__dadd_rn(fp_mul_generic(B1, A2, fc), fp_mul_generic(A1, B2, fc)), fc), fc);
+        d2[idx] = fp_store(fp_mul_generic(A1, A2, fc), fc);
+    } else if ((b1 | a1 | b2 | a2) < q || (b1 < q && a1 < q && b2 < q && a2 < q)) {
         const barrett1_t bc = make_barrett1(q, mu.x, mu.y);    // canonical operands: the one-word Barrett is exact
         d0[idx] = mul_barrett1(b1, b2, bc);
         d1[idx] = add_mod(mul_barrett1(b1, a2, bc), mul_barrett1(a1, b2, bc), q);
@@ -430,10 +438,16 @@ __global__ void trace_rescale_kernel(u64* __restrict__ Cr, u64* __restrict__ Ci,
     const int l = (int)((idx / ((size_t)n * n)) % limbs);
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
     const u64 inv = l == 0 ? inv0 : l == 1 ? inv1 : l == 2 ? inv2 : 0;
-    if (inv < q && Cr[idx] < q && Ci[idx] < q) {               // canonical operands: one-word Barrett
+    const u64 cr = Cr[idx], ci = Ci[idx];
+    if (q < (1ull << 50) && inv < q && cr < q && ci < q) {      // canonical operands, modulus below 2^50: FP64-pipe products (exact)
+        const fconst_t fc = make_fconst(q);
+        const double K = fp_load(inv);
+        Cr[idx] = fp_store(fp_mul_generic(fp_load(cr), K, fc), fc);
+        Ci[idx] = fp_store(fp_mul_generic(fp_load(ci), K, fc), fc);
+    } else if (inv < q && cr < q && ci < q) {                   // canonical operands: one-word Barrett
         const barrett1_t bc = make_barrett1(q, mu.x, mu.y);
-        Cr[idx] = mul_barrett1(Cr[idx], inv, bc);
-        Ci[idx] = mul_barrett1(Ci[idx], inv, bc);
+        Cr[idx] = mul_barrett1(cr, inv, bc);
+        Ci[idx] = mul_barrett1(ci, inv, bc);
     } else {
         Cr[idx] = mul_barrett(Cr[idx], inv, q, mu.x, mu.y);
         Ci[idx] = mul_barrett(Ci[idx], inv, q, mu.x, mu.y);
@@ -448,8 +462,16 @@ __global__ void trace_rescale_limbs_kernel(u64* __restrict__ Cr, u64* __restrict
     if (idx >= total) return;
     const int l = (int)((idx / ((size_t)n * n)) % limbs);
     const u64 q = moduli[l]; const ulonglong2 mu = mu_tab[l];
-    Cr[idx] = mul_barrett(Cr[idx], k.inv[l], q, mu.x, mu.y);
-    Ci[idx] = mul_barrett(Ci[idx], k.inv[l], q, mu.x, mu.y);
+    const u64 cr = Cr[idx], ci = Ci[idx], kv = k.inv[l];
+    if (q < (1ull << 50) && cr < q && ci < q && kv < q) {      // FP64-pipe products (exact) for moduli below 2^50
+        const fconst_t fc = make_fconst(q);
+        const double K = fp_load(kv);
+        Cr[idx] = fp_store(fp_mul_generic(fp_load(cr), K, fc), fc);
+        Ci[idx] = fp_store(fp_mul_generic(fp_load(ci), K, fc), fc);
+    } else {
+        Cr[idx] = mul_barrett(cr, kv, q, mu.x, mu.y);
+        Ci[idx] = mul_barrett(ci, kv, q, mu.x, mu.y);
+    }
 }
 cudaError_t trace_rescale_limbs_launch(u64* Cr, u64* Ci, const u64* moduli, const ulonglong2* mu, int n, int limbs, int batch,
                                        const RescaleConsts& k, cudaStream_t st) {
