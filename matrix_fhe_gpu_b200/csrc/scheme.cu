@@ -269,17 +269,27 @@ cudaError_t sample_launch(int kind, u64* out, const u64* moduli, const ulonglong
 // ---- layout -------------------------------------------------------------------------------------------
 __global__ void layout_kernel(const u64* __restrict__ in, u64* __restrict__ out, int n, int limbs, size_t total2,
                               int in_layout, int out_layout) {
-    const size_t i2 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;     // pairs of words
-    if (i2 >= total2) return;
-    const size_t idx = i2 * 2;
-    const u32 x = idx % n; const size_t t = idx / n;
-    const u32 y = t % n, wl = t / n, l = wl % limbs, w = wl / limbs;
-    const ulonglong2 v = *(const ulonglong2*)(in + row_offset(in_layout, w, l, y, n, limbs) + x);
-    *(ulonglong2*)(out + row_offset(out_layout, w, l, y, n, limbs) + x) = v;
+    // four pairs of words per thread, the four loads in flight before the first store (one pair per thread: 66 % of HBM)
+    const size_t i0 = (size_t)blockIdx.x * blockDim.x * 4 + threadIdx.x;
+    ulonglong2 v[4]; size_t dst[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const size_t i2 = i0 + (size_t)k * blockDim.x;
+        dst[k] = ~(size_t)0;
+        if (i2 >= total2) continue;
+        const size_t idx = i2 * 2;
+        const u32 x = idx % n; const size_t t = idx / n;
+        const u32 y = t % n, wl = t / n, l = wl % limbs, w = wl / limbs;
+        v[k] = *(const ulonglong2*)(in + row_offset(in_layout, w, l, y, n, limbs) + x);
+        dst[k] = row_offset(out_layout, w, l, y, n, limbs) + x;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (dst[k] != ~(size_t)0) *(ulonglong2*)(out + dst[k]) = v[k];
 }
 cudaError_t layout_launch(const u64* in, u64* out, int n, int limbs, int phi, int in_layout, int out_layout, cudaStream_t st) {
     const size_t total2 = (size_t)phi * limbs * n * n / 2;
-    layout_kernel<<<(unsigned)((total2 + 255) / 256), 256, 0, st>>>(in, out, n, limbs, total2, in_layout, out_layout);
+    layout_kernel<<<(unsigned)((total2 + 1023) / 1024), 256, 0, st>>>(in, out, n, limbs, total2, in_layout, out_layout);
     return cudaGetLastError();
 }
 
