@@ -241,14 +241,14 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
     const BconvScatter& tab = sc ? *sc : none;
     // tensor-core form (bconv_umma.cuh) whenever the coefficient count tiles by 128; MFHE_BCONV_PATH=c keeps the CUDA-core kernels
     const char* path = getenv("MFHE_BCONV_PATH");
-    // It pays from about 16 input limbs on (B200, N = 2^17, 16 output limbs, batch 16, ms per conversion; profiles/r2_14_bconv_umma.txt):
+    // It pays from 16 input limbs on (B200, N = 2^17, 16 output limbs, batch 16, ms per conversion; profiles/r2_14_bconv_umma.txt):
     //   input limbs      6      8      12     16     24     48
     //   CUDA cores     0.23   0.28   0.37   0.46   0.66   2.41 (no register-resident form beyond 24 limbs)
-    //   tensor cores   0.44   0.44   0.44   0.44   0.53   0.72
+    //   tensor cores   0.40   0.40   0.40   0.42   0.50   0.67
     // below that the digit recombination (NDA + NDB - 1 partial sums per output) and the per-tile hand-offs cost more than the
     // few multiply-accumulates they replace.  MFHE_BCONV_PATH=t forces the tensor-core kernel for any window, =c the CUDA cores.
     const bool force_t = path && path[0] == 't';
-    if (N % UB_M == 0 && !(path && path[0] == 'c') && !generic && (in_count > 16 || force_t)) {
+    if (N % UB_M == 0 && !(path && path[0] == 'c') && !generic && (in_count >= 16 || force_t)) {
         uint64_t pmax = 0;
         for (uint64_t v : b->p) pmax = std::max(pmax, v);
         UbArgs a;
@@ -256,7 +256,7 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
         a.l_out = b->l_out; a.q = b->d_q; a.qhat_inv = b->d_qhat_inv; a.qhat_mod_p = b->d_qhat_mod_p; a.p = b->d_p; a.mu_p = b->d_mu_p;
         a.nda = ub_digits(qmax - 1); a.ndb = ub_digits(pmax - 1); a.kp = (in_count + 31) / 32 * 32;
         a.tiles_per_item = (int)(N / UB_M); a.ntiles = (int)(batch * (N / UB_M));
-        const int smem = a.nda * UB_M * a.kp + a.ndb * UB_UN * a.kp + 512;
+        const int smem = a.nda * UB_M * a.kp + a.ndb * UB_UN * a.kp + 512 + 24 * b->l_out;
         if (smem <= 220 * 1024 && batch * (N / UB_M) < (1u << 30)) {
             int sms = 0, dev = 0;
             cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

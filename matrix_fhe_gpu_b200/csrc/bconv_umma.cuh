@@ -23,6 +23,10 @@
 
 namespace {
 constexpr int UB_M = 128, UB_UN = 16, UB_TH = 256;
+#ifndef MFHE_UB_G
+#define MFHE_UB_G 2      // A/B on B200 (48 / 24 / 12 input limbs): 2 -> 0.669 / 0.498 / 0.401 ms, 4 -> 0.686 / 0.502 / 0.418, 8 -> 0.675 / 0.557 / 0.465
+#endif
+constexpr int UB_G = MFHE_UB_G;                          // 4-limb groups (x 4 loads) a staging thread keeps in flight
 
 __device__ __forceinline__ u32 ub_smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void ub_mbar_init(u32 bar, u32 count) {
@@ -51,6 +55,11 @@ __device__ __forceinline__ void ub_commit(u32 bar) {
 __device__ __forceinline__ void ub_ld4(u32 taddr, u32 (&r)[4]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
+__device__ __forceinline__ void ub_ld8(u32 taddr, u32 (&r)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(taddr));
 }
 // byte offset of (row, k) in a canonical K-major operand whose rows hold KP bytes
 __device__ __forceinline__ u32 ub_canon(u32 row, u32 k, u32 kp) { return (row >> 3) * (8 * kp) + (k >> 4) * 128 + (row & 7) * 16 + (k & 15); }
@@ -82,7 +91,9 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
     unsigned char* ctrl = sB + (size_t)ndb * UB_UN * kp;
     const u32 bar = ub_smem_u32(ctrl);
     volatile u32* tmem_slot = reinterpret_cast<volatile u32*>(ctrl + 16);
+    u64* spc = reinterpret_cast<u64*>(ctrl + 64);            // [l_out][3]: p_j and floor(2^128 / p_j), read by the fold
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    for (int j = t; j < a.l_out; j += UB_TH) { const ulonglong2 m = a.mu_p[j]; spc[3 * j] = a.p[j]; spc[3 * j + 1] = m.x; spc[3 * j + 2] = m.y; }
 
     if (t == 0) {
         ub_mbar_init(bar, 1);
@@ -107,6 +118,12 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
     for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x) {
         const size_t b = (size_t)(tile / a.tiles_per_item), d0 = (size_t)(tile % a.tiles_per_item) * UB_M;
         const u64* x = a.in + b * (size_t)a.in_count * a.N + d0 + sc_;
+#ifdef MFHE_UB_TIMING
+        long long tk[8]; tk[0] = clock64();
+#define UB_TICK(k) tk[k] = clock64()
+#else
+#define UB_TICK(k)
+#endif
         // ---- stage A: y digits of 128 coefficients x in_count limbs; four 4-limb groups (16 loads) in flight per thread ----
         {   // the next tile of this CTA towards L2: 128 coefficients = 8 lines per limb
             const int nt = tile + (int)gridDim.x;
@@ -116,16 +133,16 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(xn + (size_t)(e >> 3) * a.N + (e & 7) * 16));
             }
         }
-        for (int kb = half; kb < kp / 4; kb += 8) {           // kl = kb, kb + 2, kb + 4, kb + 6: linear 4-limb groups
-            u64 y[4][4];
+        for (int kb = half; kb < kp / 4; kb += 2 * UB_G) {    // kl = kb, kb + 2, ...: linear 4-limb groups, UB_G of them in flight
+            u64 y[UB_G][4];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < UB_G; ++g) {
                 const int kl = kb + 2 * g, i0 = 16 * (kl >> 2) + 4 * ((kl & 3) ^ rot);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) y[g][j] = (kl < kp / 4 && i0 + j < a.in_count) ? x[(size_t)(i0 + j) * a.N] : 0;
             }
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < UB_G; ++g) {
                 const int kl = kb + 2 * g, i0 = 16 * (kl >> 2) + 4 * ((kl & 3) ^ rot);
                 if (kl >= kp / 4 || i0 >= a.in_count) continue;
 #pragma unroll
@@ -143,6 +160,7 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
                 }
             }
         }
+        UB_TICK(1);
         for (int ot = 0; ot < n_ot; ++ot) {
             // ---- the matrix digits of output tile ot: stack row 16 v + jj, byte k = digit v of C[16 ot + jj][in_start + k] ----
             if (b_tile != ot) {
@@ -155,6 +173,7 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
+            UB_TICK(2);
             if (t == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const u32 a0 = ub_smem_u32(sA), b0 = ub_smem_u32(sB), sbo = 8u * kp;
@@ -176,39 +195,58 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
                 }
                 ub_commit(bar);
             }
+            UB_TICK(3);
             ub_mbar_wait(bar, phase);
             phase ^= 1;
+            UB_TICK(4);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // ---- fold: thread = coefficient d0 + 32 (warp % 4) + lane, output limbs 16 ot + 8 (warp / 4) + 0..7 ----
             const size_t d = d0 + 32 * (warp & 3) + lane;
             const u32 trow = tmem + ((u32)(32 * (warp & 3)) << 16) + (u32)((warp >> 2) * 8);
 #pragma unroll
-            for (int grp = 0; grp < 2; ++grp) {
-                u32 acc[15][4];
+            // the 15 positions in three chunks of five (value = lo5 + 2^40 mid + 2^80 top), all 8 columns of the thread per load
+            u64 part[3][8];
 #pragma unroll
-                for (int p = 0; p < 15; ++p) {
-                    if (p < npos) ub_ld4(trow + (u32)(p * UB_UN + 4 * grp), acc[p]);
-                    else { acc[p][0] = 0; acc[p][1] = 0; acc[p][2] = 0; acc[p][3] = 0; }
+            for (int c = 0; c < 3; ++c) {
+                if (5 * c >= npos) {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) part[c][e] = 0;
+                    continue;
+                }
+                u32 acc[5][8];
+#pragma unroll
+                for (int pp = 0; pp < 5; ++pp) {
+                    if (5 * c + pp < npos) ub_ld8(trow + (u32)((5 * c + pp) * UB_UN), acc[pp]);
+                    else {
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) acc[pp][e] = 0;
+                    }
                 }
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int j = UB_UN * ot + 8 * (warp >> 2) + 4 * grp + e;
-                    const u64 lo5 = ub_fold5(acc[0][e], acc[1][e], acc[2][e], acc[3][e], acc[4][e]);       // < 2^60
-                    const u64 mid = ub_fold5(acc[5][e], acc[6][e], acc[7][e], acc[8][e], acc[9][e]);       // x 2^40
-                    const u64 top = ub_fold5(acc[10][e], acc[11][e], acc[12][e], acc[13][e], acc[14][e]);  // x 2^80 (value < 2^128)
-                    const u64 xs = mid << 40;
-                    const u64 lo = lo5 + xs;
-                    const u64 hi = (mid >> 24) + (lo < xs) + (top << 16);
-                    if (j < a.l_out) {
-                        const u64 r = bconv_fold<W1>(lo, hi, a.p[j], a.mu_p[j]);
-                        if constexpr (SC) sc.base[j][b * sc.bstride[j] + d] = r;
-                        else              a.out[(b * (size_t)a.l_out + j) * a.N + d] = r;
-                    }
+                for (int e = 0; e < 8; ++e) part[c][e] = ub_fold5(acc[0][e], acc[1][e], acc[2][e], acc[3][e], acc[4][e]);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const int j = UB_UN * ot + 8 * (warp >> 2) + e;
+                const u64 xs = part[1][e] << 40;
+                const u64 lo = part[0][e] + xs;                                   // value < 2^128 (plan creation), so top < 2^48
+                const u64 hi = (part[1][e] >> 24) + (lo < xs) + (part[2][e] << 16);
+                if (j < a.l_out) {
+                    const u64 r = bconv_fold<W1>(lo, hi, spc[3 * j], make_ulonglong2(spc[3 * j + 1], spc[3 * j + 2]));
+                    if constexpr (SC) sc.base[j][b * sc.bstride[j] + d] = r;
+                    else              a.out[(b * (size_t)a.l_out + j) * a.N + d] = r;
                 }
             }
+            UB_TICK(5);
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncthreads();                                  // accumulators drained, sB free for the next output tile
+            UB_TICK(6);
+#ifdef MFHE_UB_TIMING
+            if (blockIdx.x == 5 && t == 0 && tile == 5 + 20 * (int)gridDim.x)
+                printf("tile chain (clk): stage %lld  sync %lld  issue %lld  mma-wait %lld  fold %lld  sync %lld  total %lld\n", tk[1] - tk[0],
+                       tk[2] - tk[1], tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5], tk[6] - tk[0]);
+#endif
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

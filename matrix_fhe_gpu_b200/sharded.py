@@ -206,9 +206,9 @@ class LimbShardedBconv:
         import torch
         self.plan_q.inverse_(x)
         lin = len(self.q)
-        # more than 16 input limbs and N a multiple of 128: one mfhe_bconv call runs on the tensor cores (bconv_umma.cuh,
-        # 0.72 ms at 48 -> 16 limbs against 2 x 0.66 ms + reduce for the window form below)
-        tensor = lin > 16 and self.n % 128 == 0 and os.environ.get("MFHE_BCONV_PATH", "") != "c"
+        # 16 or more input limbs and N a multiple of 128: one mfhe_bconv call runs on the tensor cores (bconv_umma.cuh,
+        # 0.67 ms at 48 -> 16 limbs against 2 x 0.66 ms + reduce for the window form below)
+        tensor = lin >= 16 and self.n % 128 == 0 and os.environ.get("MFHE_BCONV_PATH", "") != "c"
         win = 0 if tensor else next((w for w in (24, 16, 12, 8) if lin > w and lin % w == 0), 0)
         if win:
             # the register-resident, one-word-Barrett forms of the conversion kernel exist for windows of 2..24 input
