@@ -437,6 +437,28 @@ def config5_block(dev, world, rank, dist, steps=10):
            "parity": "ok" if bool(flag.item()) else "FAILED",
            "parity_check": "poly 0, every rank's output limbs, vs the CPU oracle (INTT + bConv_BEHZ + NTT restated)",
            "algorithmic_bytes_per_step": batch * n * 8 * (2 * lin + 2 * lout)}
+    if world == 1:
+        # the base conversion alone (B2: bConv_BEHZ, 48 -> 16 limbs) -- tensor-core kernel (bconv_umma.cuh) next to the CUDA-core one
+        def conv_ms(path):
+            if path:
+                os.environ["MFHE_BCONV_PATH"] = path
+            try:
+                sh.bconv.convert(x0, n, batch); torch.cuda.synchronize()
+                ev[0].record()
+                for _ in range(steps):
+                    sh.bconv.convert(x0, n, batch)
+                ev[1].record(); torch.cuda.synchronize()
+                return ev[0].elapsed_time(ev[1]) / steps
+            finally:
+                os.environ.pop("MFHE_BCONV_PATH", None)
+        ms_t, ms_c = conv_ms(None), conv_ms("c")
+        byts = batch * n * 8 * (lin + lout)
+        blk["base_conversion_48_16"] = {
+            "ms": ms_t, "ms_cuda_core_kernel": ms_c, "modular_macs_per_s": batch * n * lin * lout / (ms_t * 1e-3),
+            "roofline": {"bound": "hbm", "algorithmic_bytes": byts, "achieved": byts / (ms_t * 1e-3) / 1e9, "peak": peaks()[0],
+                         "unit": "GB/s", "frac": byts / (ms_t * 1e-3) / 1e9 / peaks()[0]},
+            "kernel": "bconv_umma_kernel (tcgen05.mma kind::i8 digit GEMM, TMEM accumulators): 128 coefficients x 16 output limbs per "
+                      "tile, K = input limbs; ms_cuda_core_kernel = bconv_kernel (128-bit lazy multiply-accumulate)"}
     if world > 1 and symm_ok:                               # the torch symmetric-memory form of the same exchange, two stream groups
         def step2():
             work.copy_(x0)
