@@ -256,7 +256,7 @@ static int bconv_run(const mfhe_bconv_plan* b, const uint64_t* in, int in_start,
         a.l_out = b->l_out; a.q = b->d_q; a.qhat_inv = b->d_qhat_inv; a.qhat_mod_p = b->d_qhat_mod_p; a.p = b->d_p; a.mu_p = b->d_mu_p;
         a.nda = ub_digits(qmax - 1); a.ndb = ub_digits(pmax - 1); a.kp = (in_count + 31) / 32 * 32;
         a.tiles_per_item = (int)(N / UB_M); a.ntiles = (int)(batch * (N / UB_M));
-        const int smem = a.nda * UB_M * a.kp + a.ndb * UB_UN * a.kp + 512 + 24 * b->l_out;
+        const int smem = a.nda * UB_M * a.kp + a.ndb * UB_UN * a.kp + 512 + 24 * (b->l_out + in_count);
         if (smem <= 220 * 1024 && batch * (N / UB_M) < (1u << 30)) {
             int sms = 0, dev = 0;
             cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -94,6 +94,11 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
     u64* spc = reinterpret_cast<u64*>(ctrl + 64);            // [l_out][3]: p_j and floor(2^128 / p_j), read by the fold
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     for (int j = t; j < a.l_out; j += UB_TH) { const ulonglong2 m = a.mu_p[j]; spc[3 * j] = a.p[j]; spc[3 * j + 1] = m.x; spc[3 * j + 2] = m.y; }
+    u64* sqc = spc + 3 * a.l_out;                            // [in_count][3]: q_i and {(Q/q_i)^-1, shoup}, read by the staging
+    for (int i = t; i < a.in_count; i += UB_TH) {
+        const tw_t w = a.qhat_inv[a.in_start + i];
+        sqc[3 * i] = a.q[a.in_start + i]; sqc[3 * i + 1] = w.x; sqc[3 * i + 2] = w.y;
+    }
 
     if (t == 0) {
         ub_mbar_init(bar, 1);
@@ -147,7 +152,7 @@ bconv_umma_kernel(const UbArgs a, const __grid_constant__ BconvScatter sc) {
                 if (kl >= kp / 4 || i0 >= a.in_count) continue;
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    if (i0 + j < a.in_count) y[g][j] = mul_shoup(y[g][j], a.qhat_inv[a.in_start + i0 + j], a.q[a.in_start + i0 + j]);
+                    if (i0 + j < a.in_count) y[g][j] = mul_shoup(y[g][j], tw_t{sqc[3 * (i0 + j) + 1], sqc[3 * (i0 + j) + 2]}, sqc[3 * (i0 + j)]);
                 const u32 off = ub_canon(sc_, i0, kp);
 #pragma unroll
                 for (int v = 0; v < 8; ++v) {
