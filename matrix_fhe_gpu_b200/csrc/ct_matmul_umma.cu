@@ -22,6 +22,7 @@
 //              Vi and q - Vi once each), then per column block: one thread issues the 4 ND instructions, commits to an
 //              mbarrier; all 16 warps read the 2ND-1 partial sums of their 32 rows x 8 columns from TMEM, recombine to 128
 //              bits, multiply by n (shift), ONE Barrett reduction, 32-byte stores.
+#include <cstdio>
 #include "ctx.h"
 #include "modmath.cuh"
 
@@ -152,6 +153,14 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
     const int rot = (sx >> 3) & 3;
 
     for (int prob = blockIdx.x; prob < nprob; prob += gridDim.x) {
+#ifdef MFHE_MM_TIMING
+        long long tk[6] = {clock64(), 0, 0, 0, 0, 0}, acc_t[4] = {0, 0, 0, 0};
+#define MM_TICK(k) tk[k] = clock64()
+#define MM_ACC(i, a, b) acc_t[i] += tk[b] - tk[a]
+#else
+#define MM_TICK(k)
+#define MM_ACC(i, a, b)
+#endif
         const int w = prob / ll.cnt, l = ll.l[prob % ll.cnt];
         const size_t base = ((size_t)w * ll.limbs + l) * CN * CN;
         const u64 q = moduli[l], q2 = 2 * q;
@@ -186,8 +195,10 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             }
         }
 
+        MM_TICK(1);                                                             // tk[1] - tk[0]: A staging
 #pragma unroll 1
         for (int vc = 0; vc < 2; ++vc) {
+            MM_TICK(2);
             // ---- B': logical row n < 64: Dr column z = n  (k < 64: Vr, k >= 64: q - Vi);  n >= 64: Di column  (Vi, Vr).
             //      Column block cb = n / 32, stack row = 32 v + n % 32 ----
             const u64* sr = Vre + vc * T + base;
@@ -222,6 +233,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // generic-proxy stores -> visible to the MMA
             __syncthreads();
+            MM_TICK(3); MM_ACC(0, 2, 3);                                        // B' staging + barrier
 
             // one thread: the 4 ND instructions of column block cb, then a commit on the block barrier
             auto issue = [&](int cb) {
@@ -257,6 +269,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
 #pragma unroll 1
             for (int cb = 0; cb < 4; ++cb) {
                 // block cb's MMAs were issued before the previous block's reductions (or just above, for cb = 0)
+                MM_TICK(2);
                 if (cb == 0) issue(0);
                 if (vc == 1 && cb < 2 && prob + (int)gridDim.x < nprob) {       // the next problem's U components
                     const int p2 = prob + (int)gridDim.x;
@@ -267,6 +280,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
                 mbar_wait(bar, phase);
                 phase ^= 1;
 #endif
+                MM_TICK(3); MM_ACC(1, 2, 3);                                    // (issue of block 0 +) wait for the block's MMAs
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
                 // ---- epilogue: warp = TMEM lane quarter (warp % 4) x 8 columns (warp / 4).  The 16x256b load shape gives a thread
@@ -310,6 +324,7 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
                         if constexpr (2 * ND - 1 > 10) vtop[4 * grp + e] = acc[grp & 1][10][e];
                     }
                 }
+                MM_TICK(4); MM_ACC(2, 3, 4);                                    // TMEM reads + fold
                 // the accumulators are in registers: the next column block's MMAs run under the reductions below
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncthreads();
@@ -335,9 +350,15 @@ ct_matmul_umma_kernel(const u64* __restrict__ Ure, const u64* __restrict__ Uim, 
                     *reinterpret_cast<ulonglong2*>(o + (size_t)(16 * (e >> 2) + 8 * ((e >> 1) & 1)) * CN) = make_ulonglong2(res[0], res[1]);
                 }
 #endif
+                MM_TICK(5); MM_ACC(3, 4, 5);                                    // barrier + issue of the next block + reductions + stores
             }
             __syncthreads();                                                    // every warp is done with this vc's B' stacks
         }
+#ifdef MFHE_MM_TIMING
+        if (blockIdx.x == 3 && t == 0 && prob == 3 + 10 * (int)gridDim.x)
+            printf("problem chain (clk): A stage %lld  B stage (2x) %lld  mma wait (8x) %lld  tmem+fold (8x) %lld  issue+reduce+store (8x) %lld  total %lld\n",
+                   tk[1] - tk[0], acc_t[0], acc_t[1], acc_t[2], acc_t[3], clock64() - tk[0]);
+#endif
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
