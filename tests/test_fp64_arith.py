@@ -20,10 +20,12 @@ def test_modmul_exact_and_bounded(q):
         assert mx <= limit, (bound16, mx)          # |t| <= q (1/2 + B/16): the schedule's fp_t
 
 
-@pytest.mark.parametrize("logn", [12, 14, 16, 17])
+@pytest.mark.parametrize("logn", [4, 6, 8, 12, 14, 16, 17])      # 4..8: the n-point networks of the matrix scheme
 def test_networks_equal_integer_oracle_and_keep_their_bounds(logn):
     n = 1 << logn
-    mods = [int(v) for v in O.get_primes(n, 50, 2)] + [int(O.get_primes(n, 45, 1)[0]), int(O.get_primes(n, 30, 1)[0])]
+    mods = [int(v) for v in O.get_primes(2 * n, 50, 2)] + [int(O.get_primes(2 * n, 45, 1)[0]), int(O.get_primes(2 * n, 30, 1)[0])]
+    if logn == 6:
+        mods += [17592186435073, 17182765057]                  # the reference's 45- and 35-bit moduli
     assert max(mods) < 2 ** 50
     t = O.PhantomTables(logn, mods)
     rng = np.random.default_rng(logn)
