@@ -27,6 +27,7 @@
 //              recombine to 128 bits, ONE Barrett reduction per output, 16-byte stores in either layout; TMEM is
 //              handed back to the issuer as soon as the last accumulator column is in registers.  No zero-fill:
 //              the first K step of a tile is issued as overwrite / accumulate pieces.
+#include <cstdio>
 #include "ctx.h"
 #include "wcrt_common.cuh"
 
@@ -215,10 +216,16 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
             const u32 idesc_full = C::idesc(ND * UN);
             int s = 0, kt = 0, it = 0;
             u32 par = 0;
+#ifdef MFHE_UMMA_TIMING
+            long long w_te = 0, w_a = 0, w_b = 0, w_refill = 0, t_all = clock64(), tq;
+#define WT(acc, stmt) do { tq = clock64(); stmt; acc += clock64() - tq; } while (0)
+#else
+#define WT(acc, stmt) stmt
+#endif
             for (int g = 0; g < my_chunks; ++g) {
-                if (kt == 0 && it > 0) mbar_wait(bar_tempty, (it - 1) & 1);      // epilogue has drained the accumulators
-                mbar_wait(bar_fullA(s), par);
-                mbar_wait(bar_fullB(s), par);
+                if (kt == 0 && it > 0) WT(w_te, mbar_wait(bar_tempty, (it - 1) & 1));      // epilogue has drained the accumulators
+                WT(w_a, mbar_wait(bar_fullA(s), par));
+                WT(w_b, mbar_wait(bar_fullB(s), par));
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const u32 sa = smem0 + (u32)s * (u32)C::STAGE, sb = sa + ND * A_PLANE;
 #pragma unroll
@@ -262,13 +269,18 @@ wcrt_umma_kernel(const WcrtArgs a, int ntiles) {
                 if (!MFHE_UMMA_LOADER_WARP) {
                     // while chunk g runs, refill the stage chunk g-1 has just released
                     if (g >= 1 && g - 1 + C::NS < my_chunks) {
-                        mbar_wait(bar_empty((g - 1) % C::NS), ((g - 1) / C::NS) & 1);
+                        WT(w_refill, mbar_wait(bar_empty((g - 1) % C::NS), ((g - 1) / C::NS) & 1));
                         issue_A(g - 1 + C::NS);
                     }
                 }
                 if (++s == C::NS) { s = 0; par ^= 1; }
                 if (++kt == kchunks) { kt = 0; ++it; }
             }
+#ifdef MFHE_UMMA_TIMING
+            if (blockIdx.x == 7)
+                printf("issuer (clk, %d chunks): total %lld  wait tmem-empty %lld  wait table (fullA) %lld  wait digits (fullB) %lld  wait previous chunk (refill) %lld\n",
+                       my_chunks, clock64() - t_all, w_te, w_a, w_b, w_refill);
+#endif
         }
         __syncwarp();
     } else if (warp < C::PROD_WARPS) {
